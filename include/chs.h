@@ -1,0 +1,187 @@
+/*
+ * chs.h -- C ABI of the B200-native batched simulator for the RL-Cattle-Herding env step.
+ *
+ * The reference (BenCooper305/RL-Cattle-Herding) has no FFI layer: its hot path is the Python
+ * method `CattleAviary.step()` / `reset()` (gym_pybullet_drones/sb3_envs/BaseAviary.py:335-465,
+ * :280-331) running one environment per process.  This library replaces that path for E
+ * independent environments at once; every entry point cites the reference interface it stands in
+ * for.  Plain pointers and sizes only (no torch types).  Conventions:
+ *   - every function returns 0 on success or a negative ChsStatus; the message is available
+ *     from chs_last_error() (thread local);
+ *   - `*_dev` pointers are CUDA device pointers owned by the caller, `*_host` are host pointers;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); chs_step and
+ *     chs_reset are asynchronous on it and perform no host synchronisation and no allocation;
+ *   - a handle is bound to one device and is not thread safe (one handle per process per GPU).
+ *
+ * Tensor layouts seen by the caller (row-major, C order):
+ *   actions     float32 [E][D][A]   D = max_drones slots, A = action width of `act_type`
+ *                                   (rows >= the env's current drone count are ignored,
+ *                                   BaseRLAviary.py:166)
+ *   obs         float32 [E][R][L]   R = obs_rows (12 = reference padding, BaseRLAviary.py:334),
+ *                                   L = 10 + 8 + 32 + ABS*A (BaseRLAviary.py:262)
+ *   reward      float32 [E]         (CTDE packing, CattleAviary.py:332)
+ *   terminated  uint8   [E]         (CattleAviary.py:422)
+ *   truncated   uint8   [E]         (CattleAviary.py:497)
+ */
+#ifndef CHS_H_
+#define CHS_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CHS_ABI_VERSION 1
+#define CHS_MAX_DRONES 12   /* GLOBAL_MAX_NUM_DRONES, BaseAviary.py:112 */
+#define CHS_NUM_STATS 16
+
+typedef enum ChsStatus {
+  CHS_OK = 0,
+  CHS_ERR_INVALID = -1,   /* bad argument / unsupported configuration */
+  CHS_ERR_CUDA = -2,      /* a CUDA runtime call failed */
+  CHS_ERR_STATE = -3,     /* call order (e.g. step before a spawn table was set) */
+  CHS_ERR_NOMEM = -4
+} ChsStatus;
+
+/* utils/enums.py:26-35 (ActionType); values are this ABI's, names the reference's */
+typedef enum ChsAct {
+  CHS_ACT_VEL = 0,        /* (N,4): xy direction, unused z, speed fraction  BaseRLAviary.py:185-222 */
+  CHS_ACT_RPM = 1,        /* (N,4): HOVER_RPM*(1+0.05a)                    BaseRLAviary.py:168-169 */
+  CHS_ACT_PID = 2,        /* (N,3): waypoint                                BaseRLAviary.py:170-184 */
+  CHS_ACT_ONE_D_RPM = 3,  /* (N,1)                                          BaseRLAviary.py:223-224 */
+  CHS_ACT_ONE_D_PID = 4   /* (N,1)                                          BaseRLAviary.py:225-234 */
+} ChsAct;
+
+typedef enum ChsPacking {
+  CHS_PACK_CTDE = 0,      /* sb3_envs: one reward / flag pair per env */
+  CHS_PACK_MARL = 1       /* rllib_envs: per-drone reward / flags (rllib_envs/MARLCattleAviary.py) */
+} ChsPacking;
+
+/* Constructor arguments: the kwargs of CattleAviary.__init__ (sb3_envs/CattleAviary.py:14-28) that
+ * matter on the DYN path, plus batching/sharding knobs.  Zero-initialise, then set struct_size. */
+typedef struct ChsParams {
+  int32_t struct_size;        /* sizeof(ChsParams) */
+  int32_t num_cattle;         /* num_cattle kwarg (M) */
+  int32_t max_drones;         /* drone slots per env, 1..12 (num_drones kwarg sizes the action space) */
+  int32_t fixed_num_drones;   /* >0: every episode has this many drones; 0: drawn per episode in
+                                 [MIN,MAX] of the start level like BaseAviary.py:307 */
+  int32_t pyb_freq;           /* 240 */
+  int32_t ctrl_freq;          /* 30 (BASELINE) or 60 (reference default) */
+  int32_t act_type;           /* ChsAct */
+  int32_t start_level;        /* curriculum level 0..7 (CattleAviary.py:62 hard-codes 7) */
+  int32_t obs_rows;           /* R: 12 (reference) or max_drones (compact); 0 -> 12 */
+  int32_t packing;            /* ChsPacking */
+  int32_t precision;          /* 0 = fp32 (product), 1 = fp64 (parity instrument) */
+  int32_t auto_reset;         /* 1: finished envs are reset inside chs_step (VecEnv semantics) */
+  int32_t aero_flags;         /* bit0 drag, bit1 ground effect, bit2 downwash (BaseAviary.py:943-1039;
+                                 not part of Physics.DYN, off by default) */
+  int32_t cattle_integrate;   /* non-reference extension: pos += vel*CTRL_TIMESTEP after flocking */
+  int32_t env_id_offset;      /* global id of local env 0 (multi-GPU sharding by env index) */
+  int32_t envs_per_block;     /* launch tuning, 0 = auto */
+  int32_t threads_per_block;  /* launch tuning, 0 = auto */
+  int32_t reserved0;
+  uint64_t seed;              /* Philox key; streams are keyed by (seed, global env id, episode) */
+} ChsParams;
+
+typedef struct ChsHandle ChsHandle;
+
+/* Derived sizes, so that callers can allocate tensors (BaseRLAviary._observationSpace :243-267,
+ * _actionSpace :106-133). */
+typedef struct ChsDims {
+  int32_t num_envs, max_drones, num_cattle;
+  int32_t action_width;       /* A */
+  int32_t obs_rows, obs_len;  /* R, L */
+  int32_t substeps;           /* K = pyb_freq / ctrl_freq */
+  int32_t action_buffer_size; /* ABS = int(0.15*ctrl_freq), BaseRLAviary.py:69 */
+  int32_t reward_width;       /* 1 (CTDE) or max_drones (MARL) */
+  int32_t envs_per_block, threads_per_block, smem_bytes;
+} ChsDims;
+
+/* Host-side, float64, env-major view of the complete simulator state: the fields
+ * `oracle/ref_harness/ref_env.capture_state` reads off the reference env.  NULL members are skipped.
+ * Used for teacher-forced parity tests and checkpoint/resume. */
+typedef struct ChsStateView {
+  double* pos;            /* [n][D][3]  BaseAviary.pos          */
+  double* quat;           /* [n][D][4]  BaseAviary.quat (xyzw)  */
+  double* rpy;            /* [n][D][3]  BaseAviary.rpy          */
+  double* vel;            /* [n][D][3]  BaseAviary.vel          */
+  double* ang_v;          /* [n][D][3]  BaseAviary.ang_v        */
+  double* rpy_rates;      /* [n][D][3]  BaseAviary.rpy_rates    */
+  double* last_rpm;       /* [n][D][4]  BaseAviary.last_clipped_action */
+  double* pid_ipos;       /* [n][D][3]  DSLPIDControl.integral_pos_e */
+  double* pid_last_rpy;   /* [n][D][3]  DSLPIDControl.last_rpy  */
+  double* pid_irpy;       /* [n][D][3]  DSLPIDControl.integral_rpy_e */
+  double* cattle_pos;     /* [n][M][3]  */
+  double* cattle_vel;     /* [n][M][3]  */
+  double* prev_cent_dist; /* [n]  CattleAviary.prev_cent_dists (NaN = None) */
+  double* spacing_clock;  /* [n]  CattleAviary.drone_spacing_clock */
+  double* ep_return;      /* [n]  running episode return (telemetry) */
+  int64_t* step_counter;  /* [n]  BaseAviary.step_counter (physics steps) */
+  int32_t* step_counter_A;/* [n]  BaseAviary.step_counter_A (control steps) */
+  int32_t* n_drones;      /* [n]  BaseAviary.NUM_DRONES */
+  int32_t* level;         /* [n]  CurriculumLearning.curriculum_level */
+  int32_t* tally;         /* [n]  CurriculumLearning.curriculum_success_tally */
+  int32_t* spawn_idx;     /* [n]  BaseAviary.Cattle_Spawn_Index */
+  int32_t* episode;       /* [n]  episodes started so far (Philox counter) */
+} ChsStateView;
+
+int chs_abi_version(void);
+const char* chs_last_error(void);
+
+/* CattleAviary.__init__ (sb3_envs/CattleAviary.py:14-105) for `num_envs` environments on CUDA
+ * device `device`.  All state lives in HBM owned by the handle. */
+int chs_create(const ChsParams* params, int32_t num_envs, int32_t device, ChsHandle** out);
+int chs_destroy(ChsHandle* h);
+int chs_get_dims(const ChsHandle* h, ChsDims* out);
+
+/* config/cattle_positions.yaml as read at BaseAviary.py:88-94: `xy_host` is
+ * float64 [n_sims][cows_per_sim][2]; cows_per_sim must be >= num_cattle. */
+int chs_set_spawn_table(ChsHandle* h, const double* xy_host, int32_t n_sims, int32_t cows_per_sim);
+
+/* BaseAviary.reset (:280-331) for the envs whose mask byte is non-zero (NULL = all).  Writes the
+ * initial observation of those envs into obs_dev (may be NULL). */
+int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_dev, void* stream);
+
+/* BaseAviary.step (:335-465): one control step of every env in ONE kernel launch.
+ * terminal_obs_dev (nullable): [E][R][L]; with auto_reset the pre-reset observation of each
+ * finished env is written there (rows of other envs are left untouched) and obs_dev receives the
+ * first observation of the new episode, as SB3's VecEnv contract requires. */
+int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, float* reward_dev,
+             uint8_t* terminated_dev, uint8_t* truncated_dev, float* terminal_obs_dev, void* stream);
+
+/* Same step with HOST buffers (what a numpy-facing VecEnv calls): actions are copied H2D from
+ * the handle's pinned staging area, results D2H, and the call returns after the stream has
+ * drained.  Terminal observations come back compacted: *n_done_host envs finished, their indices
+ * are in done_idx_host[0..n) (capacity E) and their terminal observations in
+ * terminal_obs_host[i][R][L] (capacity E rows); both may be NULL. */
+int chs_step_host(ChsHandle* h, const float* actions_host, float* obs_host, float* reward_host,
+                  uint8_t* terminated_host, uint8_t* truncated_host, int32_t* n_done_host,
+                  int32_t* done_idx_host, float* terminal_obs_host, void* stream);
+int chs_reset_host(ChsHandle* h, const uint8_t* env_mask_host, float* obs_host, void* stream);
+
+/* State injection / extraction for envs [env0, env0+count): synchronous, host float64. */
+int chs_get_state(ChsHandle* h, int32_t env0, int32_t count, ChsStateView* out_host);
+int chs_set_state(ChsHandle* h, int32_t env0, int32_t count, const ChsStateView* in_host);
+
+/* Optional integer diagnostics written by chs_step (bit-exact parity outputs): the indices of the two
+ * nearest drones per drone as ranked by _computeObs (BaseRLAviary.py:310-311), int32 [E][D][2],
+ * and the herded-cow count of evaluate_herding_effectiveness (utils/evaluation.py:100-138),
+ * int32 [E].  Pass NULL to disable. */
+int chs_set_debug_buffers(ChsHandle* h, int32_t* neighbors_dev, int32_t* herded_dev);
+
+/* Episode statistics accumulated on device since the last reset of the accumulator:
+ * float64 [CHS_NUM_STATS] = { episodes, sum return, sum length (control steps), terminated,
+ * trunc altitude, trunc collision, trunc formation, trunc boundary, trunc time limit,
+ * non-finite envs, env steps, 0... }.  Copies to stats_host (synchronous); `reset`!=0 zeroes the
+ * accumulator afterwards.  This is the vector all-reduced over NCCL once per training iteration. */
+int chs_stats(ChsHandle* h, double* stats_host, int32_t reset);
+
+/* Launch-shape override after creation (bench autotuning): envs per CTA (1,2,4,8,16,32) and threads
+ * per CTA (multiple of 32, <= 1024). */
+int chs_set_launch(ChsHandle* h, int32_t envs_per_block, int32_t threads_per_block);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* CHS_H_ */

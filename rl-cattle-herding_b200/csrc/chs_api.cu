@@ -1,0 +1,317 @@
+// C ABI of the simulator (include/chs.h): handle management, launches, host-buffer path, state I/O.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/chs.h"
+#include "chs_kernel.cuh"
+
+using namespace chs;
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                       \
+  do {                                                                                       \
+    cudaError_t err__ = (expr);                                                              \
+    if (err__ != cudaSuccess)                                                                \
+      return fail(CHS_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(err__), __FILE__, __LINE__); \
+  } while (0)
+
+static const double h_curr[k::NUM_LEVELS][k::C_NCOLS] = {CHS_CURRICULUM_ROWS};
+
+struct ChsHandle {
+  ChsParams prm;
+  KParams kp;
+  int E, device;
+  bool f64;
+  size_t tsz;                 // sizeof(T)
+  void *drone, *rpm, *cpos, *cvel, *envf, *epret, *spawn;
+  int4 *envi, *envj;
+  double* stats;
+  int *dbg_nb, *dbg_herd;
+  int threads, smem;
+  bool spawn_set;
+  // device-side buffers of the host path (allocated on first use)
+  float *d_actions, *d_obs, *d_reward, *d_termobs;
+  uint8_t *d_term, *d_trunc, *d_mask;
+  int *d_count, *d_idx;
+  int* h_count;               // pinned
+};
+
+struct DeviceGuard {
+  int prev;
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+extern "C" int chs_abi_version(void) { return CHS_ABI_VERSION; }
+extern "C" const char* chs_last_error(void) { return g_err; }
+
+static int action_width(int act) {
+  switch (act) {   // BaseRLAviary._actionSpace :115-123
+    case CHS_ACT_VEL: case CHS_ACT_RPM: return 4;
+    case CHS_ACT_PID: return 3;
+    case CHS_ACT_ONE_D_RPM: case CHS_ACT_ONE_D_PID: return 1;
+  }
+  return -1;
+}
+
+template <typename T> static SmemLayout layout_for(const KParams& kp, int G) {
+  return smem_layout<T>(kp.D, kp.M, G, kp.stage_stride);
+}
+
+static int smem_for(const ChsHandle* h, int G) {
+  return h->f64 ? layout_for<double>(h->kp, G).total : layout_for<float>(h->kp, G).total;
+}
+
+static int configure_launch(ChsHandle* h, int G, int threads) {
+  if (G < 1 || G > 32 || (G & (G - 1))) return fail(CHS_ERR_INVALID, "envs_per_block must be a power of two in 1..32");
+  if (threads < 32 || threads > 512 || (threads & 31)) return fail(CHS_ERR_INVALID, "threads_per_block must be a multiple of 32 in 32..512");
+  const int smem = smem_for(h, G);
+  if (smem > 200 * 1024) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
+  DeviceGuard dg(h->device);
+  if (h->f64) {
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  } else {
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  }
+  h->kp.G = G;
+  h->threads = threads;
+  h->smem = smem;
+  return CHS_OK;
+}
+
+extern "C" int chs_set_launch(ChsHandle* h, int32_t envs_per_block, int32_t threads_per_block) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  return configure_launch(h, envs_per_block, threads_per_block);
+}
+
+extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device, ChsHandle** out) {
+  if (!prm || !out) return fail(CHS_ERR_INVALID, "null argument");
+  if (prm->struct_size != (int32_t)sizeof(ChsParams))
+    return fail(CHS_ERR_INVALID, "ChsParams.struct_size %d != %zu (ABI mismatch)", prm->struct_size, sizeof(ChsParams));
+  if (num_envs < 1) return fail(CHS_ERR_INVALID, "num_envs must be >= 1");
+  if (prm->num_cattle < 1 || prm->num_cattle > 4096) return fail(CHS_ERR_INVALID, "num_cattle out of range");
+  if (prm->max_drones < 1 || prm->max_drones > CHS_MAX_DRONES) return fail(CHS_ERR_INVALID, "max_drones must be 1..12");
+  if (prm->ctrl_freq < 1 || prm->pyb_freq < 1 || prm->pyb_freq % prm->ctrl_freq != 0)
+    return fail(CHS_ERR_INVALID, "pyb_freq is not divisible by ctrl_freq");   // BaseAviary.py:102-103
+  const int A = action_width(prm->act_type);
+  if (A < 0) return fail(CHS_ERR_INVALID, "unknown act_type %d", prm->act_type);
+  if (prm->start_level < 0 || prm->start_level >= k::NUM_LEVELS) return fail(CHS_ERR_INVALID, "start_level must be 0..7");
+  if (prm->packing != CHS_PACK_CTDE) return fail(CHS_ERR_INVALID, "only CTDE packing is implemented in this build");
+  if (prm->aero_flags != 0) return fail(CHS_ERR_INVALID, "aero extras (drag/ground effect/downwash) are not part of Physics.DYN and not implemented yet");
+  if (prm->cattle_integrate != 0) return fail(CHS_ERR_INVALID, "cattle_integrate is not implemented yet");
+  if (prm->fixed_num_drones < 0 || prm->fixed_num_drones > prm->max_drones)
+    return fail(CHS_ERR_INVALID, "fixed_num_drones must be 0..max_drones");
+  int R = prm->obs_rows == 0 ? CHS_MAX_DRONES : prm->obs_rows;
+  if (R != CHS_MAX_DRONES && R != prm->max_drones) return fail(CHS_ERR_INVALID, "obs_rows must be 12 or max_drones");
+  int ndev = 0;
+  CUDA_TRY(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return fail(CHS_ERR_INVALID, "device %d not present (%d devices)", device, ndev);
+
+  ChsHandle* h = (ChsHandle*)calloc(1, sizeof(ChsHandle));
+  if (!h) return fail(CHS_ERR_NOMEM, "out of host memory");
+  h->prm = *prm;
+  h->E = num_envs;
+  h->device = device;
+  h->f64 = prm->precision == 1;
+  h->tsz = h->f64 ? 8 : 4;
+  KParams& kp = h->kp;
+  kp.E = num_envs; kp.D = prm->max_drones; kp.M = prm->num_cattle;
+  kp.K = prm->pyb_freq / prm->ctrl_freq; kp.A = A; kp.R = R;
+  const int ABS = (int)(0.15 * prm->ctrl_freq);                 // BaseRLAviary.py:69
+  kp.L = 10 + 4 * 2 + 16 * 2 + ABS * A;                         // BaseRLAviary.py:262
+  kp.act = prm->act_type; kp.packing = prm->packing; kp.auto_reset = prm->auto_reset ? 1 : 0;
+  kp.n_sims = 0; kp.spawn_stride = 0;
+  const double* row = h_curr[prm->start_level];
+  // fixed at construction, never refreshed on level-up (CattleAviary.py:66,72-73)
+  kp.fixed_n = prm->fixed_num_drones;
+  kp.min_n = (int)row[k::C_MIN_DRONES]; kp.max_n = (int)row[k::C_MAX_DRONES];
+  {
+    // truncated iff step_counter / CTRL_FREQ > EPISODE_LEN_SEC in float64 (CattleAviary.py:545-550)
+    const double ep = row[k::C_EP_LEN];
+    long long lim = (long long)floor(ep * prm->ctrl_freq) + 2;
+    while (lim > 0 && (double)lim / (double)prm->ctrl_freq > ep) --lim;
+    kp.trunc_step_limit = (int)lim;
+  }
+  kp.ctrl_freq = prm->ctrl_freq;
+  kp.env_id_offset = prm->env_id_offset;
+  kp.stage_stride = (kp.D * kp.L + 3) & ~3;
+  if ((kp.stage_stride & 31) == 0) kp.stage_stride += 4;
+  kp.vec4_ok = ((kp.R * kp.L) % 4 == 0) ? 1 : 0;
+  kp.cattle_integrate = 0;
+  kp.seed_lo = (uint32_t)(prm->seed & 0xffffffffu); kp.seed_hi = (uint32_t)(prm->seed >> 32);
+
+  DeviceGuard dg(device);
+  const size_t E = (size_t)num_envs, D = kp.D, M = kp.M, ts = h->tsz;
+  cudaError_t err = cudaSuccess;
+#define ALLOC0(ptr, bytes)                                                        \
+  if (err == cudaSuccess) { err = cudaMalloc((void**)&(ptr), (bytes));             \
+    if (err == cudaSuccess) err = cudaMemset((ptr), 0, (bytes)); }
+  ALLOC0(h->drone, F_COUNT * D * E * 4 * ts);
+  ALLOC0(h->rpm, D * E * 4 * ts);
+  ALLOC0(h->cpos, M * E * 2 * ts);
+  ALLOC0(h->cvel, M * E * 2 * ts);
+  ALLOC0(h->envf, E * 2 * ts);
+  ALLOC0(h->epret, E * ts);
+  ALLOC0(h->envi, E * sizeof(int4));
+  ALLOC0(h->envj, E * sizeof(int4));
+  ALLOC0(h->stats, CHS_NUM_STATS * sizeof(double));
+#undef ALLOC0
+  if (err != cudaSuccess) {
+    chs_destroy(h);
+    return fail(CHS_ERR_CUDA, "device allocation failed: %s", cudaGetErrorString(err));
+  }
+  // env scalars: level = start level, prev_cent_dist = None (NaN), everything else zero
+  {
+    std::vector<int4> ej(E);
+    for (size_t e = 0; e < E; ++e) ej[e] = make_int4(prm->start_level, 0, 0, 0);
+    err = cudaMemcpy(h->envj, ej.data(), E * sizeof(int4), cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) {
+      if (h->f64) { std::vector<double2> ef(E, make_double2(NAN, 0.0)); err = cudaMemcpy(h->envf, ef.data(), E * sizeof(double2), cudaMemcpyHostToDevice); }
+      else { std::vector<float2> ef(E, make_float2(NAN, 0.f)); err = cudaMemcpy(h->envf, ef.data(), E * sizeof(float2), cudaMemcpyHostToDevice); }
+    }
+    if (err != cudaSuccess) { chs_destroy(h); return fail(CHS_ERR_CUDA, "state initialisation failed: %s", cudaGetErrorString(err)); }
+  }
+  // launch shape: enough CTAs to cover the 148 SMs a few times over, shared memory permitting
+  int G = prm->envs_per_block, threads = prm->threads_per_block;
+  if (G == 0) {
+    G = 32;
+    while (G > 1 && (smem_for(h, G) > 64 * 1024 || (num_envs + G - 1) / G < 2 * 148)) G >>= 1;
+  }
+  if (threads == 0) threads = (G * kp.M <= 256) ? 128 : 256;
+  int rc = configure_launch(h, G, threads);
+  if (rc != CHS_OK) { chs_destroy(h); return rc; }
+  *out = h;
+  return CHS_OK;
+}
+
+extern "C" int chs_destroy(ChsHandle* h) {
+  if (!h) return CHS_OK;
+  DeviceGuard dg(h->device);
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats,
+                  h->d_actions, h->d_obs, h->d_reward, h->d_termobs, h->d_term, h->d_trunc, h->d_mask, h->d_count, h->d_idx};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (h->h_count) cudaFreeHost(h->h_count);
+  free(h);
+  return CHS_OK;
+}
+
+extern "C" int chs_get_dims(const ChsHandle* h, ChsDims* out) {
+  if (!h || !out) return fail(CHS_ERR_INVALID, "null argument");
+  out->num_envs = h->E; out->max_drones = h->kp.D; out->num_cattle = h->kp.M;
+  out->action_width = h->kp.A; out->obs_rows = h->kp.R; out->obs_len = h->kp.L;
+  out->substeps = h->kp.K; out->action_buffer_size = (int)(0.15 * h->kp.ctrl_freq);
+  out->reward_width = 1;
+  out->envs_per_block = h->kp.G; out->threads_per_block = h->threads; out->smem_bytes = h->smem;
+  return CHS_OK;
+}
+
+extern "C" int chs_set_spawn_table(ChsHandle* h, const double* xy, int32_t n_sims, int32_t cows_per_sim) {
+  if (!h || !xy) return fail(CHS_ERR_INVALID, "null argument");
+  if (n_sims < 1 || cows_per_sim < h->kp.M)
+    return fail(CHS_ERR_INVALID, "spawn table needs >= 1 simulation and >= num_cattle (%d) cows per simulation, got %d x %d",
+                h->kp.M, n_sims, cows_per_sim);   // the reference raises IndexError here
+  DeviceGuard dg(h->device);
+  CUDA_TRY(cudaDeviceSynchronize());
+  if (h->spawn) { cudaFree(h->spawn); h->spawn = nullptr; }
+  const size_t n = (size_t)n_sims * cows_per_sim;
+  CUDA_TRY(cudaMalloc(&h->spawn, n * 2 * h->tsz));
+  if (h->f64) {
+    CUDA_TRY(cudaMemcpy(h->spawn, xy, n * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  } else {
+    std::vector<float> f(n * 2);
+    for (size_t i = 0; i < n * 2; ++i) f[i] = (float)xy[i];
+    CUDA_TRY(cudaMemcpy(h->spawn, f.data(), n * 2 * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  h->kp.n_sims = n_sims; h->kp.spawn_stride = cows_per_sim;
+  // spawn row cursor keyed by the GLOBAL env id so that results do not depend on the sharding
+  std::vector<int4> ei((size_t)h->E);
+  CUDA_TRY(cudaMemcpy(ei.data(), h->envi, ei.size() * sizeof(int4), cudaMemcpyDeviceToHost));
+  for (int e = 0; e < h->E; ++e) ei[e].w = (int)(((long long)h->kp.env_id_offset + e) % n_sims);
+  CUDA_TRY(cudaMemcpy(h->envi, ei.data(), ei.size() * sizeof(int4), cudaMemcpyHostToDevice));
+  h->spawn_set = true;
+  return CHS_OK;
+}
+
+extern "C" int chs_set_debug_buffers(ChsHandle* h, int32_t* neighbors_dev, int32_t* herded_dev) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  h->dbg_nb = neighbors_dev; h->dbg_herd = herded_dev;
+  return CHS_OK;
+}
+
+template <typename T> static KArgs<T> base_args(ChsHandle* h) {
+  KArgs<T> a;
+  memset(&a, 0, sizeof(a));
+  a.p = h->kp;
+  a.drone = (typename VT<T>::v4*)h->drone; a.rpm = (typename VT<T>::v4*)h->rpm;
+  a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
+  a.envi = h->envi; a.envj = h->envj; a.envf = (typename VT<T>::v2*)h->envf; a.epret = (T*)h->epret;
+  a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats;
+  a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd;
+  return a;
+}
+
+static bool aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
+
+template <typename T>
+static int launch_reset(ChsHandle* h, const uint8_t* mask_dev, float* obs_dev, cudaStream_t st) {
+  KArgs<T> a = base_args<T>(h);
+  a.reset_mask = mask_dev; a.obs = obs_dev;
+  const int grid = (h->E + h->kp.G - 1) / h->kp.G;
+  reset_kernel<T><<<grid, h->threads, h->smem, st>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  return CHS_OK;
+}
+
+extern "C" int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_dev, void* stream) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  if (!h->spawn_set) return fail(CHS_ERR_STATE, "chs_set_spawn_table must be called before chs_reset");
+  if (obs_dev && h->kp.vec4_ok && !aligned16(obs_dev)) return fail(CHS_ERR_INVALID, "obs_dev must be 16-byte aligned");
+  DeviceGuard dg(h->device);
+  return h->f64 ? launch_reset<double>(h, env_mask_dev, obs_dev, (cudaStream_t)stream)
+                : launch_reset<float>(h, env_mask_dev, obs_dev, (cudaStream_t)stream);
+}
+
+template <typename T>
+static int launch_step(ChsHandle* h, const float* actions, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
+                       float* term_obs, int term_mode, int* term_count, int* term_idx, cudaStream_t st) {
+  KArgs<T> a = base_args<T>(h);
+  a.actions = actions; a.obs = obs; a.reward = reward; a.terminated = term; a.truncated = trunc;
+  a.term_obs = term_obs; a.term_mode = term_obs ? term_mode : 0; a.term_count = term_count; a.term_idx = term_idx;
+  const int grid = (h->E + h->kp.G - 1) / h->kp.G;
+  step_kernel<T><<<grid, h->threads, h->smem, st>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  return CHS_OK;
+}
+
+extern "C" int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, float* reward_dev,
+                        uint8_t* terminated_dev, uint8_t* truncated_dev, float* terminal_obs_dev, void* stream) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  if (!actions_dev || !reward_dev || !terminated_dev || !truncated_dev)
+    return fail(CHS_ERR_INVALID, "actions, reward, terminated and truncated pointers are required");
+  if (h->kp.auto_reset && !h->spawn_set) return fail(CHS_ERR_STATE, "auto_reset needs a spawn table");
+  if (h->kp.vec4_ok && ((obs_dev && !aligned16(obs_dev)) || (terminal_obs_dev && !aligned16(terminal_obs_dev))))
+    return fail(CHS_ERR_INVALID, "obs buffers must be 16-byte aligned");
+  DeviceGuard dg(h->device);
+  return h->f64 ? launch_step<double>(h, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
+                                      terminal_obs_dev, 1, nullptr, nullptr, (cudaStream_t)stream)
+                : launch_step<float>(h, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
+                                     terminal_obs_dev, 1, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+#include "chs_api_io.inc"

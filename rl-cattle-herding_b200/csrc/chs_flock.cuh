@@ -1,0 +1,113 @@
+// Herd update: MathUtils + MathematicalFlock terms (utils/flockUtils.py:11-58,116-160,237-374) as driven by
+// BaseAviary._flockingStep (sb3_envs/BaseAviary.py:1352-1400).  Scalar device functions; the kernel maps
+// one (env, cow) pair per thread with the herd staged in shared memory.
+#pragma once
+#include "chs_layout.cuh"
+
+namespace chs {
+
+// MathUtils.bump_function (flockUtils.py:31-39), same assignment order: NaN -> 0
+template <typename T> __device__ __forceinline__ T bump(T z) {
+  if (z < T(0)) return T(0);
+  if (z < T(k::BUMP_H)) return T(1);
+  if (z <= T(1)) return T(0.5) * (T(1) + Mth<T>::cospi((z - T(k::BUMP_H)) * T(1.0 / (1.0 - k::BUMP_H))));
+  return T(0);
+}
+
+// One neighbour's contribution to C2*(gradient + consensus) for displacement d = q_j - q_i and relative
+// velocity dp = p_j - p_i:  phi_alpha(sigma_norm(d)) * sigma_norm_grad(d) + bump(sigma_norm(d)/r) * dp
+// with a = b = 5, c = 0 and r == d (flockUtils.py:41-58,327-337,365-374).
+template <typename T>
+__device__ __forceinline__ void lattice_term(T dx, T dy, T dpx, T dpy, T sigma_r, T& gx, T& gy, T& cx, T& cy) {
+  const T r2 = dx * dx + dy * dy;
+  const T s = Mth<T>::sqrt(T(1) + T(k::EPS) * r2);
+  const T sn = r2 / (s + T(1));                 // == (s - 1)/eps without the cancellation
+  const T b = bump<T>(sn / sigma_r);
+  const T zz = sn - sigma_r;
+  const T phi = T(k::PHI_HALF_AB) * zz / Mth<T>::sqrt(T(1) + zz * zz);
+  const T w = b * phi / s;
+  gx += w * dx; gy += w * dy;
+  cx += b * dpx; cy += b * dpy;
+}
+
+// alpha term of cow i over every other cow (flockUtils.py:237-258); the herd is read from shared memory
+// at stride G (cow-major, env-minor).  Returns C2_alpha*(grad + cons).
+template <typename T>
+__device__ __forceinline__ void alpha_term(const typename VT<T>::v2* s_cpos, const typename VT<T>::v2* s_cvel,
+                                           int i, int g, int G, int M, T& ux, T& uy) {
+  const auto qi = s_cpos[i * G + g];
+  const auto pi = s_cvel[i * G + g];
+  T gx = 0, gy = 0, cx = 0, cy = 0;
+  for (int j = 0; j < M; ++j) {
+    if (j == i) continue;
+    const auto qj = s_cpos[j * G + g];
+    const T dx = qj.x - qi.x, dy = qj.y - qi.y;
+    // compact support: bump(sigma_norm(d)/sigma_norm(1.2)) == 0 for |d| >= 1.2, and it reaches 0
+    // continuously, so skipping r^2 >= 1.44 changes nothing (sensing range 999 never bites).
+    // A NaN distance fails the test and is propagated like in the reference.
+    if (dx * dx + dy * dy >= T(k::ALPHA_RANGE * k::ALPHA_RANGE)) continue;
+    const auto pj = s_cvel[j * G + g];
+    lattice_term<T>(dx, dy, pj.x - pi.x, pj.y - pi.y, T(k::SIGMA_ALPHA), gx, gy, cx, cy);
+  }
+  ux = T(k::C2_ALPHA) * gx + T(k::C2_ALPHA) * cx;
+  uy = T(k::C2_ALPHA) * gy + T(k::C2_ALPHA) * cy;
+}
+
+// shepherd (delta) interaction + predator repulsion + gamma term of cow i (flockUtils.py:271-323,343-348,
+// 150-160), then the velocity update and speed clip of BaseAviary.py:1384-1395.  `ua` is the alpha term.
+template <typename T>
+__device__ __forceinline__ typename VT<T>::v2 herd_finish(const typename VT<T>::v4* s_dpos, int n, int g, int G,
+                                                          typename VT<T>::v2 qi, typename VT<T>::v2 pi, T uax, T uay) {
+  T ux = uax, uy = uay;
+  if (n > 0) {
+    T gx = 0, gy = 0, cx = 0, cy = 0, px = 0, py = 0;
+    for (int kk = 0; kk < n; ++kk) {
+      const auto yk = s_dpos[kk * G + g];
+      const T ex = qi.x - yk.x, ey = qi.y - yk.y;            // diff = q_i - y_k
+      const T r = Mth<T>::sqrt(ex * ex + ey * ey);
+      const T dist = r + T(1e-6);
+      const T mu = Mth<T>::min(dist / T(k::SHEPHERD_R), T(1));
+      const T ax = ex / dist, ay = ey / dist;
+      const T ap = ax * pi.x + ay * pi.y;
+      const T pikx = mu * (pi.x - ax * ap), piky = mu * (pi.y - ay * ap);   // mu * (I - a a^T) p_i
+      const T om = T(1) - mu;                                 // q_ik - q_i = (1-mu)(y_k - q_i)
+      lattice_term<T>(-om * ex, -om * ey, pikx - pi.x, piky - pi.y, T(k::SIGMA_BETA), gx, gy, cx, cy);
+      if (r <= T(k::DANGER_RANGE)) {                          // -k (y_k - q_i)/|.|^3 ; r == 0 -> NaN like numpy
+        const T inv = T(k::PREDATOR_K) / (r * r * r);
+        px += inv * ex; py += inv * ey;
+      }
+    }
+    ux += T(k::C2_BETA) * gx + T(k::C2_BETA) * cx;
+    uy += T(k::C2_BETA) * gy + T(k::C2_BETA) * cy;
+    ux += px; uy += py;
+  }
+  {  // gamma: -C1*sigma_1(q_i - target) - C2*p_i, target = scalar 1 broadcast
+    const T zx = qi.x - T(k::CONSENSUS), zy = qi.y - T(k::CONSENSUS);
+    ux += -T(k::C1_GAMMA) * (zx / Mth<T>::sqrt(T(1) + zx * zx)) - T(k::C2_GAMMA) * pi.x;
+    uy += -T(k::C1_GAMMA) * (zy / Mth<T>::sqrt(T(1) + zy * zy)) - T(k::C2_GAMMA) * pi.y;
+  }
+  T vx = pi.x + ux * T(k::FLOCK_DT2), vy = pi.y + uy * T(k::FLOCK_DT2);
+  const T sp = Mth<T>::sqrt(vx * vx + vy * vy);
+  if (sp > T(k::MAX_VEL_CATTLE)) { const T f = T(k::MAX_VEL_CATTLE) / sp; vx *= f; vy *= f; }
+  return mk2<T>(vx, vy);
+}
+
+// evaluate_herding_effectiveness for one cow: winding number w.r.t. the polygon drones[0..n-1] in index
+// order (utils/evaluation.py:100-138,271-273).  Returns 1 if the cow is inside.
+template <typename T>
+__device__ __forceinline__ int cow_inside(const typename VT<T>::v4* s_dpos, int n, int g, int G, T px, T py) {
+  int wn = 0;
+  if (n <= 0) return 0;
+  auto a = s_dpos[g];
+  for (int i = 0; i < n; ++i) {
+    const int i2 = (i + 1 == n) ? 0 : i + 1;
+    const auto b = s_dpos[i2 * G + g];
+    const T il = (b.x - a.x) * (py - a.y) - (px - a.x) * (b.y - a.y);
+    if (a.y <= py) { if (b.y > py && il > T(0)) ++wn; }
+    else           { if (b.y <= py && il < T(0)) --wn; }
+    a = b;
+  }
+  return wn != 0;
+}
+
+}  // namespace chs

@@ -1,0 +1,408 @@
+// The fused env-step kernel and the masked reset kernel.
+//
+// One CTA owns G consecutive environments (G = 1..32, power of two).  Inside a phase every thread takes
+// flat (entity, env) items with the env index fastest, so lanes of a warp touch consecutive environments:
+// HBM accesses are coalesced along the env axis and shared-memory accesses are conflict free.
+//
+//   phase 0  zero the obs staging area, stage the herd (pos, vel) in shared memory, read env scalars,
+//            build the list of envs whose herd updates this step (step_counter_A even, BaseAviary.py:454)
+//   phase 1  "drone" threads: action -> PID -> K DYN substeps in registers, state written back to HBM
+//            "worker" threads (all others), concurrently: alpha-lattice term of the herd update, which
+//            does not depend on the drones
+//   phase 2  drone threads: neighbour ranking, spacing / cattle-distance reward pieces, obs row pieces
+//            all threads: shepherd + predator + gamma terms, herd velocity write-back; winding numbers
+//   phase 3  one thread per env: reward, terminated (x2, stateful), truncated, counters, statistics
+//   phase 4  coalesced copy of the staged observation rows (and zero padding) to the obs tensor
+//   phase 5  (only CTAs with a finished env, auto_reset) reset those envs in place and emit their first obs
+#pragma once
+#include "chs_drone.cuh"
+#include "chs_flock.cuh"
+#include "chs_task.cuh"
+
+namespace chs {
+
+template <typename T> struct Smem {
+  typename VT<T>::v4* dpos;
+  typename VT<T>::v4* redA;
+  typename VT<T>::v4* redB;
+  typename VT<T>::v2* cpos;
+  typename VT<T>::v2* cvel;
+  typename VT<T>::v2* u;
+  float* stage;
+  int* n; int* herd; int* done; int* newn; int* row; int* flist; int* termrow; int* dlist; int* epi;
+  int* misc;   // [0] number of flock-active envs, [1] number of finished envs
+};
+
+template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* base, const KParams& p) {
+  const SmemLayout l = smem_layout<T>(p.D, p.M, p.G, p.stage_stride);
+  Smem<T> s;
+  s.dpos = reinterpret_cast<typename VT<T>::v4*>(base + l.off_dpos);
+  s.redA = reinterpret_cast<typename VT<T>::v4*>(base + l.off_redA);
+  s.redB = reinterpret_cast<typename VT<T>::v4*>(base + l.off_redB);
+  s.cpos = reinterpret_cast<typename VT<T>::v2*>(base + l.off_cpos);
+  s.cvel = reinterpret_cast<typename VT<T>::v2*>(base + l.off_cvel);
+  s.u = reinterpret_cast<typename VT<T>::v2*>(base + l.off_u);
+  s.stage = reinterpret_cast<float*>(base + l.off_stage);
+  int* ib = reinterpret_cast<int*>(base + l.off_int);
+  s.n = ib + 32 * I_N; s.herd = ib + 32 * I_HERD; s.done = ib + 32 * I_DONE; s.newn = ib + 32 * I_NEWN;
+  s.row = ib + 32 * I_ROW; s.flist = ib + 32 * I_FLOCK; s.termrow = ib + 32 * I_TERMROW; s.dlist = ib + 32 * I_DLIST; s.epi = ib + 32 * I_EPI;
+  s.misc = ib + 32 * I_COUNT;
+  return s;
+}
+
+__device__ __forceinline__ int ilog2_pow2(int g) { return 31 - __clz(g); }
+
+// Copies the staged rows of env g (plus zero padding up to R*L floats) to dst, one warp per env.
+__device__ __forceinline__ void copy_rows(const KParams& p, const float* stage_g, float* dst, int lane) {
+  const int RL = p.R * p.L;
+  if (p.vec4_ok) {
+    const float4* src4 = reinterpret_cast<const float4*>(stage_g);
+    float4* dst4 = reinterpret_cast<float4*>(dst);
+    const int nq = RL >> 2, sq = p.stage_stride >> 2;
+    for (int r = lane; r < nq; r += 32) {
+      const float4 v = (r < sq) ? src4[r] : make_float4(0.f, 0.f, 0.f, 0.f);
+      __stcs(dst4 + r, v);
+    }
+  } else {
+    const int DL = p.D * p.L;
+    for (int r = lane; r < RL; r += 32) __stcs(dst + r, r < DL ? stage_g[r] : 0.f);
+  }
+}
+
+// Draws of one reset (BaseAviary.py:307 and :617,631), keyed by (seed, global env id, episode).
+__device__ __forceinline__ int draw_num_drones(const KParams& p, int gid, int episode) {
+  if (p.fixed_n > 0) return p.fixed_n;
+  uint32_t c[4] = {(uint32_t)gid, (uint32_t)episode, 0u, (uint32_t)TAG_NDRONES};
+  philox4x32_10(c, p.seed_lo, p.seed_hi);
+  const int span = p.max_n - p.min_n + 1;
+  int n = p.min_n + (int)(u01_24(c[0]) * span);
+  return n > p.D ? p.D : n;
+}
+
+// Phase 5 / reset kernel body: in-place reset of the envs listed in s.dlist[0..nd) and emission of their
+// first observation (BaseAviary.reset :280-331, _housekeeping :547-637, initialize_drone_positions
+// :251-277).  PID state, prev_cent_dist, the spacing clock and the curriculum survive.
+// Must be called by every thread of the CTA; `nd` is CTA-uniform.
+template <typename T>
+__device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0, int nd) {
+  const KParams& p = a.p;
+  const int t = threadIdx.x, nt = blockDim.x, G = p.G, E = p.E;
+  __syncthreads();   // the copy-out of the terminal observations has finished reading the staging area
+  const int sq = p.stage_stride >> 2;
+  for (int it = t; it < nd * sq; it += nt) {
+    const int g = s.dlist[it / sq];
+    reinterpret_cast<float4*>(s.stage + (size_t)g * p.stage_stride)[it % sq] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  // cows: table position, velocity 0.2*(cos th, sin th), th = pi*(2u-1) (BaseAviary.py:611-637)
+  for (int it = t; it < nd * p.M; it += nt) {
+    const int g = s.dlist[it % nd], j = it / nd, e = e0 + g;
+    const auto xy = a.spawn[(size_t)s.row[g] * p.spawn_stride + j];
+    uint32_t c[4] = {(uint32_t)(p.env_id_offset + e), (uint32_t)s.epi[g] /* new episode index */, (uint32_t)j,
+                     (uint32_t)TAG_COW};
+    philox4x32_10(c, p.seed_lo, p.seed_hi);
+    // c[0] stands for the yaw draw (unused on the DYN path), c[1] for the velocity angle
+    T sn, cs;
+    Mth<T>::sincospi(T(2.0 * u01_24(c[1]) - 1.0), &sn, &cs);
+    const auto v = mk2<T>(T(k::MAX_VEL_CATTLE) * cs, T(k::MAX_VEL_CATTLE) * sn);
+    a.cpos[(size_t)j * E + e] = xy;
+    a.cvel[(size_t)j * E + e] = v;
+    s.cpos[j * G + g] = xy;
+  }
+  // drones: line / two-row spawn at z = 0.45 (BaseAviary.py:251-277); every slot's kinematics zeroed
+  for (int it = t; it < nd * p.D; it += nt) {
+    const int g = s.dlist[it % nd], d = it / nd, e = e0 + g;
+    const int n = s.newn[g];
+    DroneState<T> ds;
+    load_drone<T>(a, d, e, ds);     // keeps the PID fields
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { ds.p[i] = 0; ds.v[i] = 0; ds.w[i] = 0; ds.rpy[i] = 0; ds.av[i] = 0; }
+    ds.q[0] = ds.q[1] = ds.q[2] = ds.q[3] = 0;
+    if (d < n) {
+      int col = d;
+      T y = 0;
+      if (n > 4) { const int n1 = n / 2; if (d >= n1) { col = d - n1; y = T(k::DRONE_SPAWN_SPACING); } }
+      ds.p[0] = T(col) * T(k::DRONE_SPAWN_SPACING); ds.p[1] = y; ds.p[2] = T(k::TARGET_ALT);
+      ds.q[3] = T(1);
+      s.stage[(size_t)g * p.stage_stride + d * p.L] = (float)ds.p[2];
+    }
+    store_drone<T>(a, d, e, ds);
+    a.rpm[(size_t)d * E + e] = mk4<T>(0, 0, 0, 0);
+    s.dpos[d * G + g] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], T(0));
+    if (d == 0) s.n[g] = n;
+  }
+  __syncthreads();
+  for (int it = t; it < nd * p.D; it += nt) {
+    const int g = s.dlist[it % nd], d = it / nd;
+    const int n = s.n[g];
+    if (d < n) drone_reduce<T>(p, g, d, n, 0, false, s.dpos, s.cpos, s.redA, s.redB, s.stage, nullptr);
+  }
+  __syncthreads();
+  if (a.obs) {
+    const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
+    for (int i = warp; i < nd; i += nwarp) {
+      const int g = s.dlist[i];
+      copy_rows(p, s.stage + (size_t)g * p.stage_stride, a.obs + (size_t)(e0 + g) * p.R * p.L, lane);
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512) reset_kernel(const KArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const KParams& p = a.p;
+  Smem<T> s = carve<T>(smem_raw, p);
+  const int t = threadIdx.x, G = p.G, E = p.E;
+  const int e0 = blockIdx.x * G;
+  if (t < 32) {
+    bool sel = false;
+    const int e = e0 + t;
+    if (t < G && e < E && (a.reset_mask == nullptr || a.reset_mask[e])) {
+      sel = true;
+      int4 ei = a.envi[e];
+      int4 ej = a.envj[e];
+      ej.z += 1;                                         // episode index
+      const int n = draw_num_drones(p, p.env_id_offset + e, ej.z);
+      int row = ei.w + 1;                                // Cattle_Spawn_Index pre-increment with wrap (:600-603)
+      if (row >= p.n_sims) row = 0;
+      a.envi[e] = make_int4(0, 0, n, row);
+      a.envj[e] = ej;
+      a.epret[e] = T(0);
+      s.newn[t] = n; s.row[t] = row; s.epi[t] = ej.z;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, sel);
+    if (sel) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
+    if (t == 0) s.misc[1] = __popc(m);
+  }
+  __syncthreads();
+  const int nd = s.misc[1];
+  if (nd > 0) reset_envs<T>(a, s, e0, nd);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const KParams& p = a.p;
+  Smem<T> s = carve<T>(smem_raw, p);
+  const int t = threadIdx.x, nt = blockDim.x, G = p.G, E = p.E, D = p.D, M = p.M;
+  const int lg = ilog2_pow2(G);
+  const int e0 = blockIdx.x * G;
+  const T ctrl_dt = T(1.0) / T(p.ctrl_freq);
+  const T pyb_dt = T(1.0) / T(p.ctrl_freq * p.K);
+
+  // ---------------- phase 0 ----------------
+  {
+    const int nq = (G * p.stage_stride) >> 2;
+    float4* st4 = reinterpret_cast<float4*>(s.stage);
+    for (int i = t; i < nq; i += nt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int it = t; it < M * G; it += nt) {
+      const int g = it & (G - 1), j = it >> lg, e = e0 + g;
+      if (e < E) { s.cpos[it] = a.cpos[(size_t)j * E + e]; s.cvel[it] = a.cvel[(size_t)j * E + e]; }
+      else { s.cpos[it] = mk2<T>(0, 0); s.cvel[it] = mk2<T>(0, 0); }
+    }
+    if (t < 32) {
+      bool fl = false;
+      const int e = e0 + t;
+      if (t < G) {
+        int n = 0;
+        if (e < E) { const int4 ei = a.envi[e]; n = ei.z; fl = (((ei.y + 1) & 1) == 0); }
+        s.n[t] = n; s.herd[t] = 0; s.done[t] = 0;
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, fl);
+      if (fl) s.flist[__popc(m & ((1u << t) - 1u))] = t;
+      if (t == 0) { s.misc[0] = __popc(m); s.misc[1] = 0; }
+    }
+  }
+  __syncthreads();
+
+  // ---------------- phase 1 ----------------
+  const int DG = D * G;
+  int ndt = (DG + 31) & ~31;
+  if (ndt > nt) ndt = nt;
+  const int nact = s.misc[0];
+  if (t < ndt) {
+    for (int it = t; it < DG; it += ndt) {
+      const int g = it & (G - 1), d = it >> lg, e = e0 + g;
+      if (e < E && d < s.n[g]) {
+        DroneState<T> ds;
+        load_drone<T>(a, d, e, ds);
+        T rpm[4];
+        action_to_rpm<T>(p, ds, a.actions + ((size_t)e * D + d) * p.A, ctrl_dt, rpm);
+        dyn_substeps<T>(ds, rpm, p.K, pyb_dt);
+        store_drone<T>(a, d, e, ds);
+        a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
+        s.dpos[it] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], T(0));
+        // own-state part of the obs row (BaseRLAviary.py:286-297): z, rpy, vel, ang_v
+        float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
+        row[0] = (float)ds.p[2];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { row[1 + i] = (float)ds.rpy[i]; row[4 + i] = (float)ds.v[i]; row[7 + i] = (float)ds.av[i]; }
+      }
+    }
+  }
+  {
+    const int wt0 = (ndt < nt) ? ndt : 0;
+    const int nw = nt - wt0;
+    if (t >= wt0) {
+      for (int it = t - wt0; it < nact * M; it += nw) {
+        const int g = s.flist[it % nact], i = it / nact;
+        T ux, uy;
+        alpha_term<T>(s.cpos, s.cvel, i, g, G, M, ux, uy);
+        s.u[i * G + g] = mk2<T>(ux, uy);
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---------------- phase 2 ----------------
+  if (t < ndt) {
+    for (int it = t; it < DG; it += ndt) {
+      const int g = it & (G - 1), d = it >> lg, e = e0 + g;
+      const int n = s.n[g];
+      if (e < E && d < n) {
+        const int level = a.envj[e].x;
+        drone_reduce<T>(p, g, d, n, level, true, s.dpos, s.cpos, s.redA, s.redB, s.stage,
+                        a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr);
+      }
+    }
+  }
+  for (int it = t; it < nact * M; it += nt) {
+    const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
+    const auto ua = s.u[i * G + g];
+    const auto v = herd_finish<T>(s.dpos, s.n[g], g, G, s.cpos[i * G + g], s.cvel[i * G + g], ua.x, ua.y);
+    a.cvel[(size_t)i * E + e] = v;       // positions are not advanced on the DYN path
+  }
+  for (int it = t; it < M * G; it += nt) {
+    const int g = it & (G - 1);
+    const int n = s.n[g];
+    if (n > 0) {
+      const auto c = s.cpos[it];
+      if (cow_inside<T>(s.dpos, n, g, G, c.x, c.y)) atomicAdd(&s.herd[g], 1);
+    }
+  }
+  __syncthreads();
+
+  // ---------------- phase 3 ----------------
+  if (t < 32) {
+    bool fin = false;
+    const int e = e0 + t;
+    if (t < G && e < E) {
+      const int n = s.n[t];
+      const int4 ei = a.envi[e];
+      int4 ej = a.envj[e];
+      auto ef = a.envf[e];
+      int level = ej.x;
+      const int level_in = level;
+      // sums in the reference's order: drone by drone, nearest neighbour first (CattleAviary.py:231-247)
+      T ssum = 0, csum = 0, c2d = 0, ms = Mth<T>::inf(), dcx = 0, dcy = 0;
+      bool alt_bad = false, isolated = false;
+      for (int d = 0; d < n; ++d) {
+        const auto A = s.redA[d * G + t];
+        const auto B = s.redB[d * G + t];
+        const auto P = s.dpos[d * G + t];
+        csum += A.z; ssum += A.x; csum += A.w; ssum += A.y;
+        c2d += B.x;
+        ms = Mth<T>::min(ms, B.y);
+        isolated = isolated || (B.y > T(k::MAX_FORMATION_DISTANCE));
+        alt_bad = alt_bad || (B.z != T(0));
+        dcx += P.x; dcy += P.y;
+      }
+      csum /= (T(n) * T(2.0)); ssum /= (T(n) * T(2.0)); c2d /= T(n);
+      dcx /= T(n); dcy /= T(n);
+      T ccx = 0, ccy = 0;
+      for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + t]; ccx += c.x; ccy += c.y; }
+      ccx /= T(M); ccy /= T(M);
+      const T ddx = dcx - ccx, ddy = dcy - ccy;
+      const T cent = Mth<T>::sqrt(ddx * ddx + ddy * ddy + T(0));
+      T approach = 0;
+      if (ef.x == ef.x) {   // prev_cent_dists is not None
+        const T change = ef.x - cent;
+        approach = clipv<T>((change / T(k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * T(5), T(-1), T(1));
+      }
+      ef.x = cent;
+      const int herded = s.herd[t];
+      const T eff = (M > 0) ? T(herded) / T(M) * T(100) : T(0);
+      const T r_global = ssum * curr<T>(level, k::C_W_SIMPLE) + csum * curr<T>(level, k::C_W_COMPLEX) +
+                         T(0.1) * curr<T>(level, k::C_W_SURV) + approach * curr<T>(level, k::C_W_APPROACH) +
+                         (eff / T(100)) * curr<T>(level, k::C_W_EFF) + c2d * curr<T>(level, k::C_W_C2D);
+      // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
+      const bool term1 = compute_terminated<T>(level, ms, cent, eff, ef.y);
+      if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
+        ej.y += 1;
+        if (ej.y >= (int)c_curr[level_in][k::C_REQ_TALLY]) {
+          ej.y = 0;
+          level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
+        }
+      }
+      ej.x = level;
+      // second call, the one step() returns (BaseAviary.py:458)
+      const bool term = compute_terminated<T>(level, ms, cent, eff, ef.y);
+      // _computeTruncated (:497-552), first hit in the reference's order
+      int cause = -1;
+      if (alt_bad) cause = 0;
+      else if (ms < T(k::COLLISION_THRESHOLD)) cause = 1;
+      else if (isolated) cause = 2;
+      else if (cent > T(k::MISSION_BOUNDARY)) cause = 3;
+      else if (ei.x > p.trunc_step_limit) cause = 4;
+      const bool trunc = cause >= 0;
+      a.reward[e] = (float)r_global;
+      a.terminated[e] = term ? 1 : 0;
+      a.truncated[e] = trunc ? 1 : 0;
+      if (a.dbg_herded) a.dbg_herded[e] = herded;
+      T epret = a.epret[e] + r_global;
+      int sc = ei.x + p.K, scA = ei.y + 1, nn = n, row = ei.w;
+      fin = term || trunc;
+      if (!(r_global == r_global) || Mth<T>::abs(r_global) == Mth<T>::inf()) atomicAdd(a.stats + 9, 1.0);
+      if (fin) {
+        atomicAdd(a.stats + 0, 1.0);
+        atomicAdd(a.stats + 1, (double)epret);
+        atomicAdd(a.stats + 2, (double)scA);
+        if (term) atomicAdd(a.stats + 3, 1.0);
+        if (trunc) atomicAdd(a.stats + 4 + cause, 1.0);
+      }
+      if (fin && p.auto_reset) {
+        ej.z += 1;
+        nn = draw_num_drones(p, p.env_id_offset + e, ej.z);
+        row = ei.w + 1;
+        if (row >= p.n_sims) row = 0;
+        sc = 0; scA = 0; epret = 0;
+        s.done[t] = 1; s.newn[t] = nn; s.row[t] = row; s.epi[t] = ej.z;
+        int trow = 0;
+        if (a.term_mode == 2) { trow = atomicAdd(a.term_count, 1); a.term_idx[trow] = e; }
+        s.termrow[t] = trow;
+      } else {
+        fin = false;
+      }
+      a.envi[e] = make_int4(sc, scA, nn, row);
+      a.envj[e] = ej;
+      a.envf[e] = ef;
+      a.epret[e] = epret;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, fin);
+    if (fin) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
+    if (t == 0) { s.misc[1] = __popc(m); if (blockIdx.x == 0) atomicAdd(a.stats + 10, (double)E); }
+  }
+  __syncthreads();
+
+  // ---------------- phase 4 ----------------
+  const int nd = s.misc[1];
+  {
+    const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
+    const size_t RL = (size_t)p.R * p.L;
+    for (int g = warp; g < G; g += nwarp) {
+      const int e = e0 + g;
+      if (e >= E) break;
+      float* dst = a.obs ? a.obs + (size_t)e * RL : nullptr;
+      if (s.done[g]) {
+        dst = nullptr;
+        if (a.term_obs) dst = a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[g] : (size_t)e) * RL;
+      }
+      if (dst) copy_rows(p, s.stage + (size_t)g * p.stage_stride, dst, lane);
+    }
+  }
+  // ---------------- phase 5 ----------------
+  if (nd > 0) {
+    reset_envs<T>(a, s, e0, nd);
+  }
+}
+
+}  // namespace chs

@@ -1,0 +1,91 @@
+// HBM state layout and the kernel argument block.
+//
+// All persistent state is structure-of-arrays with the ENV INDEX FASTEST, so that a warp whose lanes
+// are consecutive environments moves 512 B (float4) / 256 B (float2) fully coalesced lines:
+//   drone   v4 [7][D][E]   A: pos.xyz | roll      B: quat.xyzw       C: vel.xyz | pitch
+//                          D: rpy_rates.xyz | yaw E: pid_ipos.xyz | ang_v.x
+//                          F: pid_last_rpy.xyz | ang_v.y             G: pid_irpy.xyz | ang_v.z
+//                          (exactly the 28 per-drone floats the reference keeps: BaseAviary.py:704-721
+//                           kinematics + DSLPIDControl.py:65-78 controller state)
+//   rpm     v4 [D][E]      last_clipped_action (BaseAviary.py:450), write-only on the DYN path
+//   cpos    v2 [M][E]      cattle xy (z is the constant 0.1; cattle never move in DYN)
+//   cvel    v2 [M][E]      cattle xy velocity (z = 0)
+//   envi  int4 [E]         step_counter, step_counter_A, n_drones, spawn_idx
+//   envj  int4 [E]         level, tally, episode, reserved
+//   envf    v2 [E]         prev_cent_dist (NaN = None), spacing_clock
+//   epret    T [E]         running episode return (telemetry)
+#pragma once
+#include "chs_math.cuh"
+#include "../../include/chs.h"
+
+namespace chs {
+
+enum DroneField { F_A = 0, F_B, F_C, F_D, F_E, F_F, F_G, F_COUNT };
+
+struct KParams {
+  int E, D, M, K, A, R, L;
+  int act, packing, auto_reset;
+  int G;                 // envs per CTA (1..32, power of two)
+  int n_sims, spawn_stride;
+  int fixed_n, min_n, max_n;
+  int trunc_step_limit;  // truncated iff step_counter > this  (step_counter/CTRL_FREQ > EPISODE_LEN_SEC)
+  int ctrl_freq;
+  int env_id_offset;
+  int stage_stride;      // floats per env in the obs staging area (>= D*L, multiple of 4)
+  int vec4_ok;           // (R*L) % 4 == 0 -> float4 copy-out
+  int cattle_integrate;
+  uint32_t seed_lo, seed_hi;
+};
+
+template <typename T> struct KArgs {
+  KParams p;
+  typename VT<T>::v4* drone;
+  typename VT<T>::v4* rpm;
+  typename VT<T>::v2* cpos;
+  typename VT<T>::v2* cvel;
+  int4* envi;
+  int4* envj;
+  typename VT<T>::v2* envf;
+  T* epret;
+  const typename VT<T>::v2* spawn;   // [n_sims][spawn_stride]
+  double* stats;                     // [CHS_NUM_STATS]
+  // per-call
+  const float* actions;              // [E][D][A]
+  float* obs;                        // [E][R][L]
+  float* reward;                     // [E] (CTDE) / [E][D] (MARL)
+  uint8_t* terminated;
+  uint8_t* truncated;
+  float* term_obs;                   // nullable: full [E][R][L] (term_mode 1) or compact rows (mode 2)
+  int term_mode;
+  int* term_count;                   // mode 2: atomic row counter
+  int* term_idx;                     // mode 2: env index of each compact row
+  const uint8_t* reset_mask;         // reset kernel only (nullable = all)
+  int* dbg_neighbors;                // nullable [E][D][2]
+  int* dbg_herded;                   // nullable [E]
+};
+
+// ---- shared-memory carve-up (per CTA of G envs) ----------------------------------------------------
+struct SmemLayout {
+  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_int, total;
+};
+
+template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, int M, int G, int stage_stride) {
+  SmemLayout s;
+  int o = 0;
+  const int v4 = 4 * (int)sizeof(T), v2 = 2 * (int)sizeof(T);
+  s.off_dpos = o; o += D * G * v4;
+  s.off_redA = o; o += D * G * v4;
+  s.off_redB = o; o += D * G * v4;
+  s.off_cpos = o; o += M * G * v2;
+  s.off_cvel = o; o += M * G * v2;
+  s.off_u = o;    o += M * G * v2;
+  o = (o + 15) & ~15;
+  s.off_stage = o; o += G * stage_stride * 4;
+  s.off_int = o;  o += (9 * 32 + 8) * 4;   // nine per-env int arrays [32] + misc
+  s.total = o;
+  return s;
+}
+
+enum IntSlot { I_N = 0, I_HERD = 1, I_DONE = 2, I_NEWN = 3, I_ROW = 4, I_FLOCK = 5, I_TERMROW = 6, I_DLIST = 7, I_EPI = 8, I_COUNT = 9 };
+
+}  // namespace chs

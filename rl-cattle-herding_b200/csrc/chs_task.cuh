@@ -1,0 +1,129 @@
+// Task layer: reward shapes, success / truncation tests and observation pieces of
+// sb3_envs/CattleAviary.py:213-332,422-552,572-679 and sb3_envs/BaseRLAviary.py:272-342.
+#pragma once
+#include "chs_layout.cuh"
+
+namespace chs {
+
+__constant__ double c_curr[k::NUM_LEVELS][k::C_NCOLS] = {CHS_CURRICULUM_ROWS};
+
+template <typename T> __device__ __forceinline__ T curr(int level, int col) { return T(c_curr[level][col]); }
+
+// CattleAviary.SimpleSpacingReward (:594-626)
+template <typename T> __device__ __forceinline__ T simple_spacing(T r, T desired, T tolfrac) {
+  const T tol = desired * tolfrac;
+  const T lo = desired - tol, hi = desired + tol;
+  if (lo <= r && r <= hi) return T(1);
+  if (r < lo) return T(-1) + (r / lo) * T(2);
+  if (r > hi) return T(1) - ((r - hi) / (T(7.0) - hi)) * T(2);
+  return T(-1);
+}
+
+// CattleAviary.DroneSpacingRewardFunction (:630-667)
+template <typename T> __device__ __forceinline__ T complex_spacing(T r, T d_star) {
+  const T zz = (r - d_star) / T(0.4 + 1e-9);
+  const T gauss = Mth<T>::exp(T(-0.5) * zz * zz);
+  const T coll = (r < T(0.3)) ? T(-1.0) * (T(1.0) - (r / T(0.3 + 1e-9))) : T(0);
+  const T pull = (r > T(1.5)) ? T(-0.3) * (r - T(1.5)) / T(5.0 - 1.5) : T(0);
+  return gauss + coll + pull + T(0.1) * (T(1) - Mth<T>::abs(r - d_star));
+}
+
+// CattleAviary.CattleSpacingRewardFunction (:572-592)
+template <typename T> __device__ __forceinline__ T cattle_spacing(T r) {
+  if (r <= T(k::SP_R0)) {
+    const T a = r - T(k::SP_D);
+    return T(k::SP_A) * Mth<T>::exp(-(a * a) / T(2 * k::SP_C * k::SP_C)) -
+           T(k::SP_B) * Mth<T>::exp(-(r * r) / T(2 * k::SP_K * k::SP_K));
+  }
+  // g(r0)/exp(-lam*r0) * exp(-lam*r); the prefactor is a constant of the shape parameters
+  return T(2.662959707043491) * Mth<T>::exp(T(-k::SP_LAM) * r);
+}
+
+// Per-drone results handed from the (env, drone) threads to the per-env combine through shared memory.
+//   redA = (simple(d1), simple(d2), complex(d1), complex(d2))
+//   redB = (cattle_spacing(min cow distance), d1 = distance to the nearest other drone, altitude-violation flag, 0)
+
+// Everything one drone contributes to the observation row and to the reward/flag reductions.
+//   obs row (BaseRLAviary.py:286-334): [z rpy vel ang_v | rel-xy of the 2 nearest drones, stable order |
+//   zeros up to 12 neighbour slots | rel-xy of cows 0..15 | zeros]; only the neighbour and cattle parts are
+//   written here (the own-state part is written by the thread that integrated the drone).
+template <typename T>
+__device__ __forceinline__ void drone_reduce(const KParams& p, int g, int d, int n, int level, bool want_reward,
+                                             const typename VT<T>::v4* s_dpos, const typename VT<T>::v2* s_cpos,
+                                             typename VT<T>::v4* s_redA, typename VT<T>::v4* s_redB,
+                                             float* s_stage, int* dbg_nb /* nullable: [2] */) {
+  const int G = p.G;
+  const auto me = s_dpos[d * G + g];
+  // two nearest other drones; strict '<' keeps index order on ties (stable sort, :310-311)
+  T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
+  int j1 = -1, j2 = -1;
+  for (int j = 0; j < n; ++j) {
+    if (j == d) continue;
+    const auto o = s_dpos[j * G + g];
+    const T dx = o.x - me.x, dy = o.y - me.y;
+    const T dist = Mth<T>::sqrt(dx * dx + dy * dy);
+    if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
+    else if (dist < d2) { d2 = dist; j2 = j; }
+  }
+  // a NaN distance never wins '<'; numpy's stable argsort puts NaN last as well
+  float* row = s_stage + (size_t)g * p.stage_stride + d * p.L;
+  const int nb_slots = (p.L - 10) / 2;       // row truncated to L (BaseRLAviary.py:336-340)
+  if (j1 >= 0 && nb_slots > 0) {
+    const auto o = s_dpos[j1 * G + g];
+    row[10] = (float)(o.x - me.x); row[11] = (float)(o.y - me.y);
+  }
+  if (j2 >= 0 && nb_slots > 1) {
+    const auto o = s_dpos[j2 * G + g];
+    row[12] = (float)(o.x - me.x); row[13] = (float)(o.y - me.y);
+  }
+  if (dbg_nb) { dbg_nb[0] = j1; dbg_nb[1] = j2; }
+  // cattle: relative xy of cows 0..15 into the row, minimum distance over ALL cows for the reward
+  T m2 = Mth<T>::inf();
+  const int cbase = 10 + 2 * CHS_MAX_DRONES;   // neighbours are padded to 12 slots, not 4 (:313-314)
+  for (int j = 0; j < p.M; ++j) {
+    const auto c = s_cpos[j * G + g];
+    const T dx = c.x - me.x, dy = c.y - me.y;
+    if (j < 16) {
+      const int col = cbase + 2 * j;
+      if (col + 1 < p.L) { row[col] = (float)dx; row[col + 1] = (float)dy; }
+      else if (col < p.L) { row[col] = (float)dx; }
+    }
+    m2 = Mth<T>::min(m2, dx * dx + dy * dy);
+  }
+  if (want_reward) {
+    const T desired = curr<T>(level, k::C_DESIRED), tolf = curr<T>(level, k::C_TOL);
+    s_redA[d * G + g] = mk4<T>(simple_spacing<T>(d1, desired, tolf), simple_spacing<T>(d2, desired, tolf),
+                               complex_spacing<T>(d1, desired), complex_spacing<T>(d2, desired));
+    const T alt_bad = (Mth<T>::abs(me.z - T(k::TARGET_ALT)) > T(k::MAX_ALT_ERROR)) ? T(1) : T(0);
+    s_redB[d * G + g] = mk4<T>(cattle_spacing<T>(Mth<T>::sqrt(m2)), d1, alt_bad, T(0));
+  }
+}
+
+// CattleAviary._computeTerminated (:422-492); stateful through the spacing clock (levels 0/1).
+// `ms` = minimum pairwise drone xy spacing, `cent` = centroid distance, `eff` = effectiveness in percent.
+template <typename T>
+__device__ __forceinline__ bool compute_terminated(int level, T ms, T cent, T eff, T& clock) {
+  if (level <= 1) {
+    const T desired = curr<T>(level, k::C_DESIRED), tol = curr<T>(level, k::C_TOL);
+    const T hi = desired + desired * tol, lo = desired - desired * tol;
+    if (ms < hi && ms > lo) {
+      clock += T(1.0 / 240.0);           // hard-coded 1/240 per CALL (:441), two calls per step
+      if (clock >= curr<T>(level, k::C_HOLD)) return true;
+    } else {
+      clock = T(0);
+    }
+  } else if (level <= 3) {
+    if (cent < curr<T>(level, k::C_APPROACH_MIN)) return true;
+  } else if (level == 4 || level == 6) {
+    if (eff > curr<T>(level, k::C_MIN_EFF)) return true;
+  } else if (level == 5) {
+    if (eff > curr<T>(level, k::C_MIN_EFF)) {
+      const T desired = curr<T>(level, k::C_CATTLE_DESIRED), tol = curr<T>(level, k::C_CATTLE_TOL);
+      const T hi = desired + desired * tol, lo = desired - desired * tol;
+      if (ms < hi && ms > lo) return true;
+    }
+  }
+  return false;   // level 7 has no branch
+}
+
+}  // namespace chs
