@@ -166,8 +166,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   ALLOC0(h->rpm, D * E * 4 * ts);
   ALLOC0(h->cpos, M * E * 2 * ts);
   ALLOC0(h->cvel, M * E * 2 * ts);
-  ALLOC0(h->envf, E * 2 * ts);
-  ALLOC0(h->epret, E * ts);
+  ALLOC0(h->envf, E * sizeof(double2));
+  ALLOC0(h->epret, E * sizeof(double));
   ALLOC0(h->envi, E * sizeof(int4));
   ALLOC0(h->envj, E * sizeof(int4));
   ALLOC0(h->stats, CHS_NUM_STATS * sizeof(double));
@@ -182,8 +182,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
     for (size_t e = 0; e < E; ++e) ej[e] = make_int4(prm->start_level, 0, 0, 0);
     err = cudaMemcpy(h->envj, ej.data(), E * sizeof(int4), cudaMemcpyHostToDevice);
     if (err == cudaSuccess) {
-      if (h->f64) { std::vector<double2> ef(E, make_double2(NAN, 0.0)); err = cudaMemcpy(h->envf, ef.data(), E * sizeof(double2), cudaMemcpyHostToDevice); }
-      else { std::vector<float2> ef(E, make_float2(NAN, 0.f)); err = cudaMemcpy(h->envf, ef.data(), E * sizeof(float2), cudaMemcpyHostToDevice); }
+      std::vector<double2> ef(E, make_double2(NAN, 0.0));
+      err = cudaMemcpy(h->envf, ef.data(), E * sizeof(double2), cudaMemcpyHostToDevice);
     }
     if (err != cudaSuccess) { chs_destroy(h); return fail(CHS_ERR_CUDA, "state initialisation failed: %s", cudaGetErrorString(err)); }
   }
@@ -260,7 +260,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.p = h->kp;
   a.drone = (typename VT<T>::v4*)h->drone; a.rpm = (typename VT<T>::v4*)h->rpm;
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
-  a.envi = h->envi; a.envj = h->envj; a.envf = (typename VT<T>::v2*)h->envf; a.epret = (T*)h->epret;
+  a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats;
   a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd;
   return a;

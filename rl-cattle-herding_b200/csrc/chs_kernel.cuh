@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(512) reset_kernel(const KArgs<T> a) {
       if (row >= p.n_sims) row = 0;
       a.envi[e] = make_int4(0, 0, n, row);
       a.envj[e] = ej;
-      a.epret[e] = T(0);
+      a.epret[e] = 0.0;
       s.newn[t] = n; s.row[t] = row; s.epi[t] = ej.z;
     }
     const unsigned m = __ballot_sync(0xffffffffu, sel);
@@ -292,40 +292,42 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       auto ef = a.envf[e];
       int level = ej.x;
       const int level_in = level;
+      // Per-env scalar arithmetic is float64 in both builds (one thread per env, ~100 flops): the approach term
+      // amplifies centroid-distance differences by 5*ctrl_freq/2.5 and the spacing clock counts in 1/240.
       // sums in the reference's order: drone by drone, nearest neighbour first (CattleAviary.py:231-247)
-      T ssum = 0, csum = 0, c2d = 0, ms = Mth<T>::inf(), dcx = 0, dcy = 0;
+      double ssum = 0, csum = 0, c2d = 0, ms = Mth<double>::inf(), dcx = 0, dcy = 0;
       bool alt_bad = false, isolated = false;
       for (int d = 0; d < n; ++d) {
         const auto A = s.redA[d * G + t];
         const auto B = s.redB[d * G + t];
         const auto P = s.dpos[d * G + t];
-        csum += A.z; ssum += A.x; csum += A.w; ssum += A.y;
-        c2d += B.x;
-        ms = Mth<T>::min(ms, B.y);
+        csum += (double)A.z; ssum += (double)A.x; csum += (double)A.w; ssum += (double)A.y;
+        c2d += (double)B.x;
+        ms = fmin(ms, (double)B.y);
         isolated = isolated || (B.y > T(k::MAX_FORMATION_DISTANCE));
         alt_bad = alt_bad || (B.z != T(0));
-        dcx += P.x; dcy += P.y;
+        dcx += (double)P.x; dcy += (double)P.y;
       }
-      csum /= (T(n) * T(2.0)); ssum /= (T(n) * T(2.0)); c2d /= T(n);
-      dcx /= T(n); dcy /= T(n);
-      T ccx = 0, ccy = 0;
-      for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + t]; ccx += c.x; ccy += c.y; }
-      ccx /= T(M); ccy /= T(M);
-      const T ddx = dcx - ccx, ddy = dcy - ccy;
-      const T cent = Mth<T>::sqrt(ddx * ddx + ddy * ddy + T(0));
-      T approach = 0;
+      csum /= (n * 2.0); ssum /= (n * 2.0); c2d /= (double)n;
+      dcx /= (double)n; dcy /= (double)n;
+      double ccx = 0, ccy = 0;
+      for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + t]; ccx += (double)c.x; ccy += (double)c.y; }
+      ccx /= (double)M; ccy /= (double)M;
+      const double ddx = dcx - ccx, ddy = dcy - ccy;
+      const double cent = sqrt(ddx * ddx + ddy * ddy + 0.0);
+      double approach = 0;
       if (ef.x == ef.x) {   // prev_cent_dists is not None
-        const T change = ef.x - cent;
-        approach = clipv<T>((change / T(k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * T(5), T(-1), T(1));
+        const double change = ef.x - cent;
+        approach = clipv<double>((change / (k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * 5.0, -1.0, 1.0);
       }
       ef.x = cent;
       const int herded = s.herd[t];
-      const T eff = (M > 0) ? T(herded) / T(M) * T(100) : T(0);
-      const T r_global = ssum * curr<T>(level, k::C_W_SIMPLE) + csum * curr<T>(level, k::C_W_COMPLEX) +
-                         T(0.1) * curr<T>(level, k::C_W_SURV) + approach * curr<T>(level, k::C_W_APPROACH) +
-                         (eff / T(100)) * curr<T>(level, k::C_W_EFF) + c2d * curr<T>(level, k::C_W_C2D);
+      const double eff = (M > 0) ? (double)herded / (double)M * 100.0 : 0.0;
+      const double r_global = ssum * c_curr[level][k::C_W_SIMPLE] + csum * c_curr[level][k::C_W_COMPLEX] +
+                              0.1 * c_curr[level][k::C_W_SURV] + approach * c_curr[level][k::C_W_APPROACH] +
+                              (eff / 100.0) * c_curr[level][k::C_W_EFF] + c2d * c_curr[level][k::C_W_C2D];
       // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
-      const bool term1 = compute_terminated<T>(level, ms, cent, eff, ef.y);
+      const bool term1 = compute_terminated<double>(level, ms, cent, eff, ef.y);
       if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
         ej.y += 1;
         if (ej.y >= (int)c_curr[level_in][k::C_REQ_TALLY]) {
@@ -335,26 +337,26 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       }
       ej.x = level;
       // second call, the one step() returns (BaseAviary.py:458)
-      const bool term = compute_terminated<T>(level, ms, cent, eff, ef.y);
+      const bool term = compute_terminated<double>(level, ms, cent, eff, ef.y);
       // _computeTruncated (:497-552), first hit in the reference's order
       int cause = -1;
       if (alt_bad) cause = 0;
-      else if (ms < T(k::COLLISION_THRESHOLD)) cause = 1;
+      else if (ms < k::COLLISION_THRESHOLD) cause = 1;
       else if (isolated) cause = 2;
-      else if (cent > T(k::MISSION_BOUNDARY)) cause = 3;
+      else if (cent > k::MISSION_BOUNDARY) cause = 3;
       else if (ei.x > p.trunc_step_limit) cause = 4;
       const bool trunc = cause >= 0;
       a.reward[e] = (float)r_global;
       a.terminated[e] = term ? 1 : 0;
       a.truncated[e] = trunc ? 1 : 0;
       if (a.dbg_herded) a.dbg_herded[e] = herded;
-      T epret = a.epret[e] + r_global;
+      double epret = a.epret[e] + r_global;
       int sc = ei.x + p.K, scA = ei.y + 1, nn = n, row = ei.w;
       fin = term || trunc;
-      if (!(r_global == r_global) || Mth<T>::abs(r_global) == Mth<T>::inf()) atomicAdd(a.stats + 9, 1.0);
+      if (!(r_global == r_global) || fabs(r_global) == Mth<double>::inf()) atomicAdd(a.stats + 9, 1.0);
       if (fin) {
         atomicAdd(a.stats + 0, 1.0);
-        atomicAdd(a.stats + 1, (double)epret);
+        atomicAdd(a.stats + 1, epret);
         atomicAdd(a.stats + 2, (double)scA);
         if (term) atomicAdd(a.stats + 3, 1.0);
         if (trunc) atomicAdd(a.stats + 4 + cause, 1.0);

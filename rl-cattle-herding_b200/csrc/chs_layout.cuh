@@ -12,8 +12,9 @@
 //   cvel    v2 [M][E]      cattle xy velocity (z = 0)
 //   envi  int4 [E]         step_counter, step_counter_A, n_drones, spawn_idx
 //   envj  int4 [E]         level, tally, episode, reserved
-//   envf    v2 [E]         prev_cent_dist (NaN = None), spacing_clock
-//   epret    T [E]         running episode return (telemetry)
+//   envf double2 [E]       prev_cent_dist (NaN = None), spacing_clock -- float64 in BOTH builds: the approach
+//                          reward multiplies a difference of two ~10 m centroid distances by 5*ctrl_freq/2.5
+//   epret double [E]       running episode return (telemetry)
 #pragma once
 #include "chs_math.cuh"
 #include "../../include/chs.h"
@@ -45,8 +46,8 @@ template <typename T> struct KArgs {
   typename VT<T>::v2* cvel;
   int4* envi;
   int4* envj;
-  typename VT<T>::v2* envf;
-  T* epret;
+  double2* envf;
+  double* epret;
   const typename VT<T>::v2* spawn;   // [n_sims][spawn_stride]
   double* stats;                     // [CHS_NUM_STATS]
   // per-call

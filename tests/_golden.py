@@ -55,3 +55,21 @@ def max_err(a, b):
     same_inf = np.isinf(a) & np.isinf(b) & (np.sign(a) == np.sign(b))
     d = np.where(both_nan | same_inf, 0.0, np.abs(a - b))
     return float(np.max(d)) if d.size else 0.0
+
+
+def near_tie_rows(pos, n, tol=2e-6):
+    """Rows (drones) whose neighbour ranking is decided by a distance gap below fp32 resolution.
+
+    `_computeObs` ranks the other drones by xy distance (BaseRLAviary.py:310-311).  The reference's line
+    spawn puts drone 1 exactly between drones 0 and 2, and ring formations are symmetric, so the top-2 order
+    can hinge on differences of ~1e-10 m that a float32 state cannot represent.  For such rows the fp32 build
+    may legitimately swap equidistant neighbours; the tests skip the neighbour columns of those rows only.
+    """
+    pos = np.asarray(pos, dtype=np.float64)[:n, :2]
+    out = np.zeros((pos.shape[0],), dtype=bool)
+    for i in range(n):
+        d = np.sort(np.delete(np.sqrt(np.sum((pos - pos[i]) ** 2, axis=1)), i))
+        gaps = np.diff(d[:3])
+        scale = np.maximum(1.0, np.abs(pos).max())
+        out[i] = bool(np.any(gaps < tol * scale))
+    return out
