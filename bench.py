@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Benchmark of the batched RL-Cattle-Herding env step (BASELINE.json: env-steps/s, device timed).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--envs-per-gpu E] [--drones 3] [--cattle 20]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference ...      # the reference algorithm's CPU port on the host cores
+
+A "step" is one control step of every environment of the batch = ONE launch of the fused CUDA kernel
+(`chs_step`).  Workload at N=1: BASELINE.json configs[1], the 3-drone / 20-cattle scene (Physics.DYN, VEL
+actions, 240 Hz physics / 30 Hz control, curriculum level 7, auto-reset) batched to 4096 envs per GPU; envs
+are sharded by index over the ranks with no collective on the step path (weak scaling: 4096 envs per GPU).
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for how each field is obtained.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--envs-per-gpu", type=int, default=4096)
+    ap.add_argument("--drones", type=int, default=3)
+    ap.add_argument("--cattle", type=int, default=20)
+    ap.add_argument("--ctrl-freq", type=int, default=30)
+    ap.add_argument("--launch", default="auto", help="'auto' or G,threads")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the bounded CPU sample")
+    return ap.parse_args()
+
+
+def algorithmic_bytes_per_env_step(n, m, rows, obs_len, act_w=4):
+    """fp32 bytes one env-step must move.  actions + drone state read/write (22 floats)
+    + last RPM + herd read + herd velocity write every 2nd step + padded obs + reward/flags + env scalars."""
+    return 4 * (n * act_w + 2 * n * 22 + n * 4 + m * 4 + 0.5 * m * 2 + rows * obs_len) + 4 + 2 + 2 * 16
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(workload_key):
+    """dram bytes per launch of the step kernel from the committed ncu capture, if one matches the workload."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(workload_key)
+    return None
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ======================================================================================================
+# CPU arm: the float64 numpy/python port of the reference algorithm (oracle/cattle_oracle.py), which is
+# pinned to the reference's own outputs by tests/test_oracle_golden.py.  The reference itself is Python and
+# needs /root/reference + pybullet, neither of which exists on the GPU box.
+# ======================================================================================================
+def _cpu_worker(args):
+    seed, n, m, ctrl_freq, budget_s, max_steps = args
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cattle_oracle as co
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("chs_spawn", os.path.join(ROOT, "rl-cattle-herding_b200", "spawn.py"))
+    spawn = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(spawn)
+    table = spawn.generate(16, m, seed=0)
+    rng = np.random.default_rng(seed)
+    env = co.OracleEnv(m, ctrl_freq=ctrl_freq, spawn_table=table, start_level=7)
+    env.reset(n, rng.random((m, 2)))
+    steps = 0
+    t0 = time.perf_counter()
+    while steps < max_steps and time.perf_counter() - t0 < budget_s:
+        a = rng.uniform(-1, 1, (n, 4)).astype(np.float32)
+        _, _, term, trunc, _ = env.step(a)
+        steps += 1
+        if term or trunc:
+            env.reset(n, rng.random((m, 2)))
+    return steps, time.perf_counter() - t0
+
+
+def cpu_env_steps_per_s(n, m, ctrl_freq, budget_s, procs):
+    if procs <= 1:
+        steps, dt = _cpu_worker((1, n, m, ctrl_freq, budget_s, 10 ** 9))
+        return steps / dt, 1, f"1 env, {steps} control steps ({dt:.1f} s), resets as they occur"
+    import multiprocessing as mp
+    with mp.get_context("fork").Pool(procs) as pool:
+        t0 = time.perf_counter()
+        res = pool.map(_cpu_worker, [(100 + i, n, m, ctrl_freq, budget_s, 10 ** 9) for i in range(procs)])
+        wall = time.perf_counter() - t0
+    steps = sum(r[0] for r in res)
+    return steps / wall, procs, f"{procs} processes x 1 env, {steps} control steps in {wall:.1f} s wall, resets as they occur"
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        pass
+    K, W = max(1, args.steps), args.warmup
+    # each "step" of this arm is a bounded sample: every process advances its env for a slice of the budget
+    budget = max(2.0, min(args.cpu_seconds * 4, 60.0))
+    value, used, sample = cpu_env_steps_per_s(args.drones, args.cattle, args.ctrl_freq, budget, cores)
+    line = {
+        "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
+        "ms_per_step": 1000.0 / value, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "impl": "reference",
+        "config": {"workload": f"{args.drones} drones / {args.cattle} cattle, Physics.DYN, VEL actions, 240 Hz / "
+                               f"{args.ctrl_freq} Hz, level 7, uniform random actions, auto-reset",
+                   "note": "CPU arm: float64 port of the reference algorithm (oracle/cattle_oracle.py, pinned to "
+                           "the reference's outputs); one env per process like SubprocVecEnv, no IPC"},
+        "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": used, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ======================================================================================================
+# GPU arm
+# ======================================================================================================
+def time_steps(env, torch, action_pool, n_steps, flush_buf, stream_sync=True):
+    """Times n_steps launches individually with CUDA events on the launching stream (torch's current stream,
+    which is the stream handed to chs_step); the L2 flush between steps is outside the event pairs."""
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(n_steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(n_steps)]
+    for i in range(n_steps):
+        if flush_buf is not None:
+            flush_buf.zero_()                      # > L2 (126 MB): evicts state and obs lines
+        starts[i].record()
+        env.step(action_pool[i % len(action_pool)])
+        ends[i].record()
+    torch.cuda.synchronize()
+    return [s.elapsed_time(e) for s, e in zip(starts, ends)]   # ms each
+
+
+def autotune_launch(env, torch, action_pool, flush_buf, candidates, reps=12):
+    best = None
+    for g, th in candidates:
+        try:
+            env.set_launch(g, th)
+        except RuntimeError:
+            continue
+        time_steps(env, torch, action_pool, 3, flush_buf)
+        ms = float(np.median(time_steps(env, torch, action_pool, reps, flush_buf)))
+        if best is None or ms < best[0]:
+            best = (ms, g, th)
+    env.set_launch(best[1], best[2])
+    return best
+
+
+def run_cuda_arm(args):
+    import torch
+    import rl_cattle_herding_b200 as pkg
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    else:
+        torch.cuda.set_device(0)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    E, N, M = args.envs_per_gpu, args.drones, args.cattle
+    K, W = args.steps, max(3, args.warmup)
+    table = pkg.spawn.generate(100 if M <= 32 else 8, M, seed=0)
+    env = pkg.CattleHerdingBatchedEnv(E, num_drones=N, num_cattle=M, ctrl_freq=args.ctrl_freq, fixed_num_drones=N,
+                                      start_level=7, auto_reset=True, spawn_table=table, device=dev.index,
+                                      env_id_offset=rank * E, seed=0)
+    gen = torch.Generator(device=dev).manual_seed(1 + rank)
+    action_pool = [torch.rand((E, N, 4), device=dev, generator=gen) * 2 - 1 for _ in range(16)]
+    flush_buf = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    env.reset()
+    torch.cuda.synchronize()
+
+    # ---- warm-up + launch-shape selection (untimed) ----
+    if args.launch == "auto":
+        cands = [(g, th) for g in (4, 8, 16, 32) for th in (128, 256)]
+        tuned = autotune_launch(env, torch, action_pool, flush_buf, cands)
+    else:
+        g, th = (int(x) for x in args.launch.split(","))
+        env.set_launch(g, th)
+        tuned = (None, g, th)
+    time_steps(env, torch, action_pool, W, flush_buf)
+    env.stats(reset=True)
+
+    # ---- timed region: exactly K steps, barrier + synchronize on both sides ----
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    with ClockSampler(dev.index) as clocks:
+        t_wall0 = time.perf_counter()
+        per_step_ms = time_steps(env, torch, action_pool, K, flush_buf)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        t_wall = time.perf_counter() - t_wall0
+    dev_ms = torch.tensor([sum(per_step_ms)], dtype=torch.float64, device=dev)
+    stats = torch.from_numpy(env.stats()).to(dev)
+    if dist is not None:
+        dist.all_reduce(dev_ms, op=dist.ReduceOp.MAX)          # max over ranks of the device time
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)           # the per-iteration episode-statistics reduction (NCCL)
+    total_ms = float(dev_ms.item())
+    ms_per_step = total_ms / K
+    value = world * E * K / (total_ms * 1e-3)
+
+    line = None
+    if rank == 0:
+        dims = env.dims
+        bytes_env = algorithmic_bytes_per_env_step(N, M, dims["obs_rows"], dims["obs_len"])
+        peak, peak_src = measured_peak_gbs()
+        achieved = bytes_env * E / (float(np.mean(per_step_ms)) * 1e-3) / 1e9
+        wl_key = f"{N}d{M}c_{E}env"
+        line = {
+            "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"CattleAviary Physics.DYN, {N} drones + {M} cattle, {E} envs per GPU, VEL actions, "
+                                   f"240 Hz physics / {args.ctrl_freq} Hz ctrl, level 7, uniform random actions, auto-reset",
+                       "envs_per_gpu": E, "total_envs": world * E, "obs_shape": [dims["obs_rows"], dims["obs_len"]],
+                       "launch": {"envs_per_block": tuned[1], "threads_per_block": tuned[2], "smem_bytes": env.dims["smem_bytes"]},
+                       "l2": "flushed between steps by zeroing a 256 MiB buffer (outside the per-step event pairs)",
+                       "timing": "sum of per-launch CUDA-event durations on the launching stream, max over ranks",
+                       "sharding": "env index, no collective on the step path; one NCCL all-reduce of the stats vector after the run"},
+            "drone_steps_per_s": value * N,
+            "wall_ms_per_step_incl_flush": t_wall * 1e3 / K,
+            "gpu_launches": K,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": recorded_traffic(wl_key), "bytes_per_env_step": bytes_env,
+                         "bytes_per_launch": bytes_env * E, "peak_source": peak_src,
+                         "kernel": "chs::step_kernel<float>", "kernel_ms": float(np.mean(per_step_ms))},
+            "clocks": clocks.summary(),
+            "episodes": {"finished": float(stats[0].item()), "mean_length": float(stats[2].item() / max(1.0, stats[0].item())),
+                         "mean_return": float(stats[1].item() / max(1.0, stats[0].item())), "non_finite": float(stats[9].item())},
+        }
+
+    # ---- e2e: the numpy-facing call (pinned host actions in, host obs/reward/flags out), per rank ----
+    if not args.no_e2e:
+        host_actions = [a.cpu().numpy() for a in action_pool[:4]]
+        for i in range(3):
+            env.step_host(host_actions[i % 4])
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        Ke = max(10, min(K, 100))
+        t0 = time.perf_counter()
+        nterm = 0
+        for i in range(Ke):
+            out = env.step_host(host_actions[i % 4])
+            nterm += len(out[4])
+        torch.cuda.synchronize()
+        e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            RL = dims["obs_rows"] * dims["obs_len"]
+            line["e2e"] = {"value": world * E * Ke / float(e2e_s.item()), "unit": "env-steps/s",
+                           "h2d_bytes_per_step": E * N * 4 * 4,
+                           "d2h_bytes_per_step": E * (RL * 4 + 4 + 2) + 4 + int(nterm / Ke * (RL * 4 + 4)),
+                           "steps": Ke, "api": "CattleHerdingBatchedEnv.step_host (chs_step_host): pinned numpy in/out"}
+
+    # ---- larger batches on the same GPU (inputs > L2, no flush needed), rank 0 of N=1 only ----
+    if rank == 0 and world == 1 and not args.no_sweep:
+        sweep = []
+        for Es in (16384, 65536, 262144):
+            if Es == E:
+                continue
+            e2 = pkg.CattleHerdingBatchedEnv(Es, num_drones=N, num_cattle=M, ctrl_freq=args.ctrl_freq, fixed_num_drones=N,
+                                             start_level=7, auto_reset=True, spawn_table=table, device=dev.index, seed=0)
+            pool2 = [torch.rand((Es, N, 4), device=dev, generator=gen) * 2 - 1 for _ in range(4)]
+            e2.reset()
+            fb = flush_buf if Es * (bytes_env + 1200) < 200e6 else None
+            best = autotune_launch(e2, torch, pool2, fb, [(g, th) for g in (8, 16, 32) for th in (128, 256)], reps=6)
+            ms = float(np.mean(time_steps(e2, torch, pool2, 30, fb)))
+            sweep.append({"envs": Es, "ms_per_step": ms, "env_steps_per_s": Es / (ms * 1e-3),
+                          "hbm_frac": bytes_env * Es / (ms * 1e-3) / 1e9 / peak, "launch": [best[1], best[2]],
+                          "l2": "flushed" if fb is not None else "working set > L2"})
+            e2.close()
+            del pool2
+        line["sweep"] = sweep
+
+    # ---- CPU baseline beside it (rank 0, N=1) ----
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, cores, sample = cpu_env_steps_per_s(N, M, args.ctrl_freq, args.cpu_seconds, 1)
+        line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    env.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_cuda_arm(args)
+
+
+if __name__ == "__main__":
+    main()
