@@ -66,15 +66,15 @@ __device__ __forceinline__ void dsl_pid(DroneState<T>& s, const T tp[3], T targe
   }
   F[2] += T(k::GRAVITY);
   const T scalar = Mth<T>::max(T(0), F[0] * R[0][2] + F[1] * R[1][2] + F[2] * R[2][2]);
-  const T thrust = (Mth<T>::sqrt(scalar / T(4 * k::KF)) - T(k::PWM2RPM_CONST)) / T(k::PWM2RPM_SCALE);
-  const T nF = Mth<T>::sqrt(F[0] * F[0] + F[1] * F[1] + F[2] * F[2]);
-  const T zb[3] = {F[0] / nF, F[1] / nF, F[2] / nF};
+  const T thrust = (Mth<T>::sqrt(scalar * T(1.0 / (4 * k::KF))) - T(k::PWM2RPM_CONST)) * T(1.0 / k::PWM2RPM_SCALE);
+  const T inF = Mth<T>::rsqrt(F[0] * F[0] + F[1] * F[1] + F[2] * F[2]);
+  const T zb[3] = {F[0] * inF, F[1] * inF, F[2] * inF};
   T sy, cy;
   Mth<T>::sincos(target_yaw, &sy, &cy);
   // zb x (cy, sy, 0)
   const T c0 = -zb[2] * sy, c1 = zb[2] * cy, c2 = zb[0] * sy - zb[1] * cy;
-  const T nc = Mth<T>::sqrt(c0 * c0 + c1 * c1 + c2 * c2);
-  const T yb[3] = {c0 / nc, c1 / nc, c2 / nc};
+  const T inc = Mth<T>::rsqrt(c0 * c0 + c1 * c1 + c2 * c2);
+  const T yb[3] = {c0 * inc, c1 * inc, c2 * inc};
   const T xb[3] = {yb[1] * zb[2] - yb[2] * zb[1], yb[2] * zb[0] - yb[0] * zb[2], yb[0] * zb[1] - yb[1] * zb[0]};
   // rot_e = vee(Rt^T R - R^T Rt) with Rt = [xb yb zb]:  A_ij = col_i(Rt) . col_j(R)
 #define CHS_DOTCOL(v, j) ((v)[0] * R[0][j] + (v)[1] * R[1][j] + (v)[2] * R[2][j])
@@ -140,7 +140,7 @@ __device__ __forceinline__ void action_to_rpm(const KParams& p, DroneState<T>& s
     if (dist <= T(1)) { tp[0] = wp[0]; tp[1] = wp[1]; tp[2] = wp[2]; }
     else {
 #pragma unroll
-      for (int i = 0; i < 3; ++i) tp[i] = s.p[i] + d[i] / dist;
+      for (int i = 0; i < 3; ++i) tp[i] = s.p[i] + d[i] / dist;   // rare branch, exact
     }
     const T tv[3] = {T(0), T(0), T(0)};
     dsl_pid<T>(s, tp, T(0), tv, ctrl_dt, cf, rpm);
@@ -167,7 +167,7 @@ __device__ __forceinline__ void dyn_substeps(DroneState<T>& s, const T rpm[4], i
     const T cr[3] = {s.w[1] * Jw[2] - s.w[2] * Jw[1], s.w[2] * Jw[0] - s.w[0] * Jw[2], s.w[0] * Jw[1] - s.w[1] * Jw[0]};
     const T wd[3] = {(tx - cr[0]) * T(1.0 / k::IXX), (ty - cr[1]) * T(1.0 / k::IYY), (tz - cr[2]) * T(1.0 / k::IZZ)};
 #pragma unroll
-    for (int i = 0; i < 3; ++i) s.v[i] = s.v[i] + dt * (fw[i] / T(k::M_KG));
+    for (int i = 0; i < 3; ++i) s.v[i] = s.v[i] + dt * (fw[i] * T(1.0 / k::M_KG));
 #pragma unroll
     for (int i = 0; i < 3; ++i) s.w[i] = s.w[i] + dt * wd[i];
 #pragma unroll
@@ -177,16 +177,16 @@ __device__ __forceinline__ void dyn_substeps(DroneState<T>& s, const T rpm[4], i
     if (!(wn <= T(1e-8))) {      // np.isclose(norm, 0): atol 1e-8
       const T pp = s.w[0], qq = s.w[1], rr = s.w[2];
       T sn, c;
-      Mth<T>::sincos(wn * dt / T(2), &sn, &c);
-      const T sc = T(2) / wn * T(0.5) * sn;
+      Mth<T>::sincos_small(wn * dt * T(0.5), &sn, &c);
+      const T sc = sn * Mth<T>::frcp(wn);        // (2/|w|) * (1/2) * sin(theta)
       const T nx = c * x + sc * (rr * y - qq * z + pp * ww);
       const T ny = c * y + sc * (-rr * x + pp * z + qq * ww);
       const T nz = c * z + sc * (qq * x - pp * y + rr * ww);
       const T nw = c * ww + sc * (-pp * x - qq * y - rr * z);
       x = nx; y = ny; z = nz; ww = nw;
     }
-    const T n = Mth<T>::sqrt(x * x + y * y + z * z + ww * ww);   // Bullet returns a unit quaternion
-    s.q[0] = x / n; s.q[1] = y / n; s.q[2] = z / n; s.q[3] = ww / n;
+    const T in = Mth<T>::rsqrt(x * x + y * y + z * z + ww * ww);   // Bullet returns a unit quaternion
+    s.q[0] = x * in; s.q[1] = y * in; s.q[2] = z * in; s.q[3] = ww * in;
   }
   // ang_v = R_prev . rpy_rates of the LAST substep (:1096-1100); earlier ones are overwritten
   if (K > 0) {

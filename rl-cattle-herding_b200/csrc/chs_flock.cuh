@@ -10,44 +10,60 @@ namespace chs {
 template <typename T> __device__ __forceinline__ T bump(T z) {
   if (z < T(0)) return T(0);
   if (z < T(k::BUMP_H)) return T(1);
-  if (z <= T(1)) return T(0.5) * (T(1) + Mth<T>::cospi((z - T(k::BUMP_H)) * T(1.0 / (1.0 - k::BUMP_H))));
+  if (z <= T(1)) return T(0.5) * (T(1) + Mth<T>::cospi_unit((z - T(k::BUMP_H)) * T(1.0 / (1.0 - k::BUMP_H))));
   return T(0);
 }
 
-// One neighbour's contribution to C2*(gradient + consensus) for displacement d = q_j - q_i and relative
+// One neighbour's contribution to (gradient + consensus) for displacement d = q_j - q_i and relative
 // velocity dp = p_j - p_i:  phi_alpha(sigma_norm(d)) * sigma_norm_grad(d) + bump(sigma_norm(d)/r) * dp
 // with a = b = 5, c = 0 and r == d (flockUtils.py:41-58,327-337,365-374).
+// sigma_norm(d) = (sqrt(1+eps r^2)-1)/eps is evaluated as r^2/(sqrt(1+eps r^2)+1): same value, no cancellation.
+// The herd update is scaled by dt^2 = 0.0025 before it reaches the velocity, so the 1-2 ulp MUFU
+// approximations of the fp32 build are far inside the parity budget.
 template <typename T>
-__device__ __forceinline__ void lattice_term(T dx, T dy, T dpx, T dpy, T sigma_r, T& gx, T& gy, T& cx, T& cy) {
+__device__ __forceinline__ void lattice_term(T dx, T dy, T dpx, T dpy, T sigma_r, T inv_sigma_r,
+                                             T& gx, T& gy, T& cx, T& cy) {
   const T r2 = dx * dx + dy * dy;
-  const T s = Mth<T>::sqrt(T(1) + T(k::EPS) * r2);
-  const T sn = r2 / (s + T(1));                 // == (s - 1)/eps without the cancellation
-  const T b = bump<T>(sn / sigma_r);
+  const T q = T(1) + T(k::EPS) * r2;
+  const T rs = Mth<T>::rsqrt(q);                // 1/sqrt(1+eps r^2)
+  const T sn = r2 * Mth<T>::frcp(q * rs + T(1));
+  const T b = bump<T>(sn * inv_sigma_r);
   const T zz = sn - sigma_r;
-  const T phi = T(k::PHI_HALF_AB) * zz / Mth<T>::sqrt(T(1) + zz * zz);
-  const T w = b * phi / s;
+  const T w = b * T(k::PHI_HALF_AB) * zz * Mth<T>::rsqrt(T(1) + zz * zz) * rs;
   gx += w * dx; gy += w * dy;
   cx += b * dpx; cy += b * dpy;
 }
 
 // alpha term of cow i over every other cow (flockUtils.py:237-258); the herd is read from shared memory
 // at stride G (cow-major, env-minor).  Returns C2_alpha*(grad + cons).
+// Compact support: bump(sigma_norm(d)/sigma_norm(1.2)) == 0 for |d| >= 1.2 and it reaches 0 continuously, so
+// pairs with r^2 >= 1.44 contribute nothing (the sensing range of 999 m never bites).  Lanes of a warp work on
+// different envs, so the in-range set differs per lane: a cheap uniform pass collects the in-range cows of a
+// 32-cow chunk in a bit mask, then every lane walks only its own set bits (a NaN distance stays in the set and
+// propagates like in the reference).
 template <typename T>
 __device__ __forceinline__ void alpha_term(const typename VT<T>::v2* s_cpos, const typename VT<T>::v2* s_cvel,
                                            int i, int g, int G, int M, T& ux, T& uy) {
   const auto qi = s_cpos[i * G + g];
   const auto pi = s_cvel[i * G + g];
   T gx = 0, gy = 0, cx = 0, cy = 0;
-  for (int j = 0; j < M; ++j) {
-    if (j == i) continue;
-    const auto qj = s_cpos[j * G + g];
-    const T dx = qj.x - qi.x, dy = qj.y - qi.y;
-    // compact support: bump(sigma_norm(d)/sigma_norm(1.2)) == 0 for |d| >= 1.2, and it reaches 0
-    // continuously, so skipping r^2 >= 1.44 changes nothing (sensing range 999 never bites).
-    // A NaN distance fails the test and is propagated like in the reference.
-    if (dx * dx + dy * dy >= T(k::ALPHA_RANGE * k::ALPHA_RANGE)) continue;
-    const auto pj = s_cvel[j * G + g];
-    lattice_term<T>(dx, dy, pj.x - pi.x, pj.y - pi.y, T(k::SIGMA_ALPHA), gx, gy, cx, cy);
+  for (int j0 = 0; j0 < M; j0 += 32) {
+    const int jn = (M - j0 < 32) ? (M - j0) : 32;
+    unsigned mask = 0;
+    for (int jj = 0; jj < jn; ++jj) {
+      const auto qj = s_cpos[(j0 + jj) * G + g];
+      const T dx = qj.x - qi.x, dy = qj.y - qi.y;
+      if (!(dx * dx + dy * dy >= T(k::ALPHA_RANGE * k::ALPHA_RANGE))) mask |= 1u << jj;
+    }
+    if (i >= j0 && i < j0 + 32) mask &= ~(1u << (i - j0));
+    while (mask) {
+      const int j = j0 + __ffs(mask) - 1;
+      mask &= mask - 1;
+      const auto qj = s_cpos[j * G + g];
+      const auto pj = s_cvel[j * G + g];
+      lattice_term<T>(qj.x - qi.x, qj.y - qi.y, pj.x - pi.x, pj.y - pi.y, T(k::SIGMA_ALPHA), T(1.0 / k::SIGMA_ALPHA),
+                      gx, gy, cx, cy);
+    }
   }
   ux = T(k::C2_ALPHA) * gx + T(k::C2_ALPHA) * cx;
   uy = T(k::C2_ALPHA) * gy + T(k::C2_ALPHA) * cy;
@@ -66,14 +82,15 @@ __device__ __forceinline__ typename VT<T>::v2 herd_finish(const typename VT<T>::
       const T ex = qi.x - yk.x, ey = qi.y - yk.y;            // diff = q_i - y_k
       const T r = Mth<T>::sqrt(ex * ex + ey * ey);
       const T dist = r + T(1e-6);
-      const T mu = Mth<T>::min(dist / T(k::SHEPHERD_R), T(1));
-      const T ax = ex / dist, ay = ey / dist;
+      const T mu = Mth<T>::min(dist * T(1.0 / k::SHEPHERD_R), T(1));
+      const T idist = Mth<T>::frcp(dist);
+      const T ax = ex * idist, ay = ey * idist;
       const T ap = ax * pi.x + ay * pi.y;
       const T pikx = mu * (pi.x - ax * ap), piky = mu * (pi.y - ay * ap);   // mu * (I - a a^T) p_i
       const T om = T(1) - mu;                                 // q_ik - q_i = (1-mu)(y_k - q_i)
-      lattice_term<T>(-om * ex, -om * ey, pikx - pi.x, piky - pi.y, T(k::SIGMA_BETA), gx, gy, cx, cy);
+      lattice_term<T>(-om * ex, -om * ey, pikx - pi.x, piky - pi.y, T(k::SIGMA_BETA), T(1.0 / k::SIGMA_BETA), gx, gy, cx, cy);
       if (r <= T(k::DANGER_RANGE)) {                          // -k (y_k - q_i)/|.|^3 ; r == 0 -> NaN like numpy
-        const T inv = T(k::PREDATOR_K) / (r * r * r);
+        const T inv = T(k::PREDATOR_K) * Mth<T>::frcp(r * r * r);
         px += inv * ex; py += inv * ey;
       }
     }
@@ -83,12 +100,12 @@ __device__ __forceinline__ typename VT<T>::v2 herd_finish(const typename VT<T>::
   }
   {  // gamma: -C1*sigma_1(q_i - target) - C2*p_i, target = scalar 1 broadcast
     const T zx = qi.x - T(k::CONSENSUS), zy = qi.y - T(k::CONSENSUS);
-    ux += -T(k::C1_GAMMA) * (zx / Mth<T>::sqrt(T(1) + zx * zx)) - T(k::C2_GAMMA) * pi.x;
-    uy += -T(k::C1_GAMMA) * (zy / Mth<T>::sqrt(T(1) + zy * zy)) - T(k::C2_GAMMA) * pi.y;
+    ux += -T(k::C1_GAMMA) * (zx * Mth<T>::rsqrt(T(1) + zx * zx)) - T(k::C2_GAMMA) * pi.x;
+    uy += -T(k::C1_GAMMA) * (zy * Mth<T>::rsqrt(T(1) + zy * zy)) - T(k::C2_GAMMA) * pi.y;
   }
   T vx = pi.x + ux * T(k::FLOCK_DT2), vy = pi.y + uy * T(k::FLOCK_DT2);
   const T sp = Mth<T>::sqrt(vx * vx + vy * vy);
-  if (sp > T(k::MAX_VEL_CATTLE)) { const T f = T(k::MAX_VEL_CATTLE) / sp; vx *= f; vy *= f; }
+  if (sp > T(k::MAX_VEL_CATTLE)) { const T f = T(k::MAX_VEL_CATTLE) / sp; vx *= f; vy *= f; }   // exact divide: feeds the state
   return mk2<T>(vx, vy);
 }
 

@@ -29,7 +29,7 @@ template <typename T> struct Smem {
   typename VT<T>::v2* cvel;
   typename VT<T>::v2* u;
   float* stage;
-  int* n; int* herd; int* done; int* newn; int* row; int* flist; int* termrow; int* dlist; int* epi;
+  int* n; int* herd; int* done; int* newn; int* row; int* flist; int* termrow; int* dlist; int* epi; int* level;
   int* misc;   // [0] number of flock-active envs, [1] number of finished envs
 };
 
@@ -45,7 +45,7 @@ template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* ba
   s.stage = reinterpret_cast<float*>(base + l.off_stage);
   int* ib = reinterpret_cast<int*>(base + l.off_int);
   s.n = ib + 32 * I_N; s.herd = ib + 32 * I_HERD; s.done = ib + 32 * I_DONE; s.newn = ib + 32 * I_NEWN;
-  s.row = ib + 32 * I_ROW; s.flist = ib + 32 * I_FLOCK; s.termrow = ib + 32 * I_TERMROW; s.dlist = ib + 32 * I_DLIST; s.epi = ib + 32 * I_EPI;
+  s.row = ib + 32 * I_ROW; s.flist = ib + 32 * I_FLOCK; s.termrow = ib + 32 * I_TERMROW; s.dlist = ib + 32 * I_DLIST; s.epi = ib + 32 * I_EPI; s.level = ib + 32 * I_LEVEL;
   s.misc = ib + 32 * I_COUNT;
   return s;
 }
@@ -190,6 +190,9 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
   const T pyb_dt = T(1.0) / T(p.ctrl_freq * p.K);
 
   // ---------------- phase 0 ----------------
+  int4 pre_i = make_int4(0, 0, 0, 0), pre_j = make_int4(0, 0, 0, 0);
+  double2 pre_f = make_double2(0.0, 0.0);
+  double pre_ret = 0.0;
   {
     const int nq = (G * p.stage_stride) >> 2;
     float4* st4 = reinterpret_cast<float4*>(s.stage);
@@ -204,8 +207,12 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       const int e = e0 + t;
       if (t < G) {
         int n = 0;
-        if (e < E) { const int4 ei = a.envi[e]; n = ei.z; fl = (((ei.y + 1) & 1) == 0); }
-        s.n[t] = n; s.herd[t] = 0; s.done[t] = 0;
+        if (e < E) {
+          // env scalars are fetched once, here, and stay in registers until phase 3
+          pre_i = a.envi[e]; pre_j = a.envj[e]; pre_f = a.envf[e]; pre_ret = a.epret[e];
+          n = pre_i.z; fl = (((pre_i.y + 1) & 1) == 0);
+        }
+        s.n[t] = n; s.herd[t] = 0; s.done[t] = 0; s.level[t] = pre_j.x;
       }
       const unsigned m = __ballot_sync(0xffffffffu, fl);
       if (fl) s.flist[__popc(m & ((1u << t) - 1u))] = t;
@@ -259,7 +266,7 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       const int n = s.n[g];
       if (e < E && d < n) {
-        const int level = a.envj[e].x;
+        const int level = s.level[g];
         drone_reduce<T>(p, g, d, n, level, true, s.dpos, s.cpos, s.redA, s.redB, s.stage,
                         a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr);
       }
@@ -287,9 +294,9 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
     const int e = e0 + t;
     if (t < G && e < E) {
       const int n = s.n[t];
-      const int4 ei = a.envi[e];
-      int4 ej = a.envj[e];
-      auto ef = a.envf[e];
+      const int4 ei = pre_i;
+      int4 ej = pre_j;
+      double2 ef = pre_f;
       int level = ej.x;
       const int level_in = level;
       // Per-env scalar arithmetic is float64 in both builds (one thread per env, ~100 flops): the approach term
@@ -308,11 +315,13 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
         alt_bad = alt_bad || (B.z != T(0));
         dcx += (double)P.x; dcy += (double)P.y;
       }
-      csum /= (n * 2.0); ssum /= (n * 2.0); c2d /= (double)n;
-      dcx /= (double)n; dcy /= (double)n;
+      const double inv_n = 1.0 / (double)n;
+      csum *= 0.5 * inv_n; ssum *= 0.5 * inv_n; c2d *= inv_n;
+      dcx *= inv_n; dcy *= inv_n;
       double ccx = 0, ccy = 0;
       for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + t]; ccx += (double)c.x; ccy += (double)c.y; }
-      ccx /= (double)M; ccy /= (double)M;
+      const double inv_m = 1.0 / (double)M;
+      ccx *= inv_m; ccy *= inv_m;
       const double ddx = dcx - ccx, ddy = dcy - ccy;
       const double cent = sqrt(ddx * ddx + ddy * ddy + 0.0);
       double approach = 0;
@@ -350,7 +359,7 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       a.terminated[e] = term ? 1 : 0;
       a.truncated[e] = trunc ? 1 : 0;
       if (a.dbg_herded) a.dbg_herded[e] = herded;
-      double epret = a.epret[e] + r_global;
+      double epret = pre_ret + r_global;
       int sc = ei.x + p.K, scA = ei.y + 1, nn = n, row = ei.w;
       fin = term || trunc;
       if (!(r_global == r_global) || fabs(r_global) == Mth<double>::inf()) atomicAdd(a.stats + 9, 1.0);

@@ -82,11 +82,11 @@ template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, i
   s.off_u = o;    o += M * G * v2;
   o = (o + 15) & ~15;
   s.off_stage = o; o += G * stage_stride * 4;
-  s.off_int = o;  o += (9 * 32 + 8) * 4;   // nine per-env int arrays [32] + misc
+  s.off_int = o;  o += (10 * 32 + 8) * 4;  // ten per-env int arrays [32] + misc
   s.total = o;
   return s;
 }
 
-enum IntSlot { I_N = 0, I_HERD = 1, I_DONE = 2, I_NEWN = 3, I_ROW = 4, I_FLOCK = 5, I_TERMROW = 6, I_DLIST = 7, I_EPI = 8, I_COUNT = 9 };
+enum IntSlot { I_N = 0, I_HERD = 1, I_DONE = 2, I_NEWN = 3, I_ROW = 4, I_FLOCK = 5, I_TERMROW = 6, I_DLIST = 7, I_EPI = 8, I_LEVEL = 9, I_COUNT = 10 };
 
 }  // namespace chs

@@ -21,8 +21,25 @@ template <typename T> __device__ __forceinline__ typename VT<T>::v2 mk2(T x, T y
 
 template <typename T> struct Mth;
 template <> struct Mth<float> {
-  static __device__ __forceinline__ float sqrt(float x) { return sqrtf(x); }
-  static __device__ __forceinline__ float rcp(float x) { return 1.0f / x; }
+  // sqrt.approx.f32: MUFU.SQRT, max relative error 2^-23 (IEEE sqrtf costs a ~10 instruction sequence)
+  static __device__ __forceinline__ float sqrt(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+  static __device__ __forceinline__ float rcp(float x) { return __frcp_rn(x); }
+  // 1-2 ulp approximations on the MUFU pipe; the fp32 parity budget is 1e-5 relative
+  static __device__ __forceinline__ float rsqrt(float x) { return rsqrtf(x); }
+  static __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+  static __device__ __forceinline__ float frcp(float x) { return __fdividef(1.0f, x); }
+  // cos(pi*x) for x in [0,1] (the bump function's argument): MUFU.COS, abs error ~5e-7
+  static __device__ __forceinline__ float cospi_unit(float x) { return __cosf(3.14159265358979f * x); }
+  // sin/cos of the half rotation angle of one 1/240 s substep (|x| < 0.5 unless the drone spins > 240 rad/s)
+  static __device__ __forceinline__ void sincos_small(float x, float* s, float* c) {
+    if (fabsf(x) < 0.5f) {
+      const float x2 = x * x;
+      *s = x * (1.0f + x2 * (-1.0f / 6.0f + x2 * (1.0f / 120.0f + x2 * (-1.0f / 5040.0f + x2 * (1.0f / 362880.0f)))));
+      *c = 1.0f + x2 * (-0.5f + x2 * (1.0f / 24.0f + x2 * (-1.0f / 720.0f + x2 * (1.0f / 40320.0f + x2 * (-1.0f / 3628800.0f)))));
+    } else {
+      sincosf(x, s, c);
+    }
+  }
   static __device__ __forceinline__ void sincos(float x, float* s, float* c) { sincosf(x, s, c); }
   static __device__ __forceinline__ void sincospi(float x, float* s, float* c) { sincospif(x, s, c); }
   static __device__ __forceinline__ float cospi(float x) { return cospif(x); }
@@ -38,6 +55,11 @@ template <> struct Mth<float> {
 template <> struct Mth<double> {
   static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
   static __device__ __forceinline__ double rcp(double x) { return 1.0 / x; }
+  static __device__ __forceinline__ double rsqrt(double x) { return 1.0 / ::sqrt(x); }
+  static __device__ __forceinline__ double fdiv(double a, double b) { return a / b; }
+  static __device__ __forceinline__ double frcp(double x) { return 1.0 / x; }
+  static __device__ __forceinline__ double cospi_unit(double x) { return ::cospi(x); }
+  static __device__ __forceinline__ void sincos_small(double x, double* s, double* c) { ::sincos(x, s, c); }
   static __device__ __forceinline__ void sincos(double x, double* s, double* c) { ::sincos(x, s, c); }
   static __device__ __forceinline__ void sincospi(double x, double* s, double* c) { ::sincospi(x, s, c); }
   static __device__ __forceinline__ double cospi(double x) { return ::cospi(x); }
@@ -60,7 +82,7 @@ template <typename T> __device__ __forceinline__ T clipv(T v, T lo, T hi) {
 // third column of getMatrixFromQuaternion(q): the body z axis in world coordinates
 template <typename T> __device__ __forceinline__ void quat_zaxis(const T q[4], T z[3]) {
   const T x = q[0], y = q[1], zz = q[2], w = q[3];
-  const T s = T(2) / (x * x + y * y + zz * zz + w * w);
+  const T s = T(2) * Mth<T>::frcp(x * x + y * y + zz * zz + w * w);
   const T xs = x * s, ys = y * s, zs = zz * s;
   z[0] = x * zs + w * ys;
   z[1] = y * zs - w * xs;
@@ -69,7 +91,7 @@ template <typename T> __device__ __forceinline__ void quat_zaxis(const T q[4], T
 
 template <typename T> __device__ __forceinline__ void quat_to_matrix(const T q[4], T R[3][3]) {
   const T x = q[0], y = q[1], z = q[2], w = q[3];
-  const T s = T(2) / (x * x + y * y + z * z + w * w);
+  const T s = T(2) * Mth<T>::frcp(x * x + y * y + z * z + w * w);
   const T xs = x * s, ys = y * s, zs = z * s;
   const T wx = w * xs, wy = w * ys, wz = w * zs;
   const T xx = x * xs, xy = x * ys, xz = x * zs;
