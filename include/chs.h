@@ -170,6 +170,10 @@ int chs_set_state(ChsHandle* h, int32_t env0, int32_t count, const ChsStateView*
  * int32 [E].  Pass NULL to disable. */
 int chs_set_debug_buffers(ChsHandle* h, int32_t* neighbors_dev, int32_t* herded_dev);
 
+/* Profiling aid: when non-NULL, thread 0 of every CTA of chs_step writes clock64() at the 7 phase boundaries
+ * of the fused kernel into int64 [grid][8] (grid = ceil(E / envs_per_block)).  NULL disables. */
+int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev);
+
 /* Episode statistics accumulated on device since the last reset of the accumulator:
  * float64 [CHS_NUM_STATS] = { episodes, sum return, sum length (control steps), terminated,
  * trunc altitude, trunc collision, trunc formation, trunc boundary, trunc time limit,

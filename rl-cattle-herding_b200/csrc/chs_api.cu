@@ -41,6 +41,7 @@ struct ChsHandle {
   int4 *envi, *envj;
   double* stats;
   int *dbg_nb, *dbg_herd;
+  long long* dbg_clock;
   int threads, smem;
   bool spawn_set;
   // device-side buffers of the host path (allocated on first use)
@@ -248,6 +249,12 @@ extern "C" int chs_set_spawn_table(ChsHandle* h, const double* xy, int32_t n_sim
   return CHS_OK;
 }
 
+extern "C" int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  h->dbg_clock = (long long*)clock_dev;
+  return CHS_OK;
+}
+
 extern "C" int chs_set_debug_buffers(ChsHandle* h, int32_t* neighbors_dev, int32_t* herded_dev) {
   if (!h) return fail(CHS_ERR_INVALID, "null handle");
   h->dbg_nb = neighbors_dev; h->dbg_herd = herded_dev;
@@ -262,7 +269,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
   a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats;
-  a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd;
+  a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd; a.dbg_clock = h->dbg_clock;
   return a;
 }
 

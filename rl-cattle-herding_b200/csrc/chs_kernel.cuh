@@ -29,6 +29,7 @@ template <typename T> struct Smem {
   typename VT<T>::v2* cvel;
   typename VT<T>::v2* u;
   float* stage;
+  double2* ccent;   // herd centroid per env
   int* n; int* herd; int* done; int* newn; int* row; int* flist; int* termrow; int* dlist; int* epi; int* level;
   int* misc;   // [0] number of flock-active envs, [1] number of finished envs
 };
@@ -43,6 +44,7 @@ template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* ba
   s.cvel = reinterpret_cast<typename VT<T>::v2*>(base + l.off_cvel);
   s.u = reinterpret_cast<typename VT<T>::v2*>(base + l.off_u);
   s.stage = reinterpret_cast<float*>(base + l.off_stage);
+  s.ccent = reinterpret_cast<double2*>(base + l.off_ccent);
   int* ib = reinterpret_cast<int*>(base + l.off_int);
   s.n = ib + 32 * I_N; s.herd = ib + 32 * I_HERD; s.done = ib + 32 * I_DONE; s.newn = ib + 32 * I_NEWN;
   s.row = ib + 32 * I_ROW; s.flist = ib + 32 * I_FLOCK; s.termrow = ib + 32 * I_TERMROW; s.dlist = ib + 32 * I_DLIST; s.epi = ib + 32 * I_EPI; s.level = ib + 32 * I_LEVEL;
@@ -134,7 +136,10 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
   for (int it = t; it < nd * p.D; it += nt) {
     const int g = s.dlist[it % nd], d = it / nd;
     const int n = s.n[g];
-    if (d < n) drone_reduce<T>(p, g, d, n, 0, false, s.dpos, s.cpos, s.redA, s.redB, s.stage, nullptr);
+    if (d < n) {
+      drone_neighbors<T>(p, g, d, n, 0, false, s.dpos, s.redA, s.redB, s.stage, nullptr);
+      drone_cattle<T>(p, g, d, false, s.dpos, s.cpos, s.redB, s.stage);
+    }
   }
   __syncthreads();
   if (a.obs) {
@@ -188,11 +193,28 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
   const int e0 = blockIdx.x * G;
   const T ctrl_dt = T(1.0) / T(p.ctrl_freq);
   const T pyb_dt = T(1.0) / T(p.ctrl_freq * p.K);
+  const int DG = D * G;
+  int ndt = (DG + 31) & ~31;          // "drone" threads: the first warps of the CTA
+  if (ndt > nt) ndt = nt;
 
+#define CHS_STAMP(i) do { if (a.dbg_clock && t == 0) a.dbg_clock[(size_t)blockIdx.x * 8 + (i)] = clock64(); } while (0)
+  CHS_STAMP(0);
   // ---------------- phase 0 ----------------
+  // Every global read the step needs is issued here, before the first barrier, so that the DRAM round trips
+  // of the herd, the env scalars and the first drone item of each drone thread overlap.
   int4 pre_i = make_int4(0, 0, 0, 0), pre_j = make_int4(0, 0, 0, 0);
   double2 pre_f = make_double2(0.0, 0.0);
   double pre_ret = 0.0;
+  DroneState<T> ds0;
+  float act0[4] = {0.f, 0.f, 0.f, 0.f};
+  const bool have0 = (t < ndt) && (t < DG) && (e0 + (t & (G - 1)) < E);
+  if (have0) {
+    const int g = t & (G - 1), d = t >> lg, e = e0 + g;
+    load_drone<T>(a, d, e, ds0);
+    const float* ap = a.actions + ((size_t)e * D + d) * p.A;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (i < p.A) act0[i] = ap[i];
+  }
   {
     const int nq = (G * p.stage_stride) >> 2;
     float4* st4 = reinterpret_cast<float4*>(s.stage);
@@ -220,20 +242,28 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
     }
   }
   __syncthreads();
+  CHS_STAMP(1);
 
   // ---------------- phase 1 ----------------
-  const int DG = D * G;
-  int ndt = (DG + 31) & ~31;
-  if (ndt > nt) ndt = nt;
   const int nact = s.misc[0];
   if (t < ndt) {
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       if (e < E && d < s.n[g]) {
         DroneState<T> ds;
-        load_drone<T>(a, d, e, ds);
+        float act[4];
+        if (it == t) {
+          ds = ds0;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) act[i] = act0[i];
+        } else {
+          load_drone<T>(a, d, e, ds);
+          const float* ap = a.actions + ((size_t)e * D + d) * p.A;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) act[i] = (i < p.A) ? ap[i] : 0.f;
+        }
         T rpm[4];
-        action_to_rpm<T>(p, ds, a.actions + ((size_t)e * D + d) * p.A, ctrl_dt, rpm);
+        action_to_rpm<T>(p, ds, act, ctrl_dt, rpm);
         dyn_substeps<T>(ds, rpm, p.K, pyb_dt);
         store_drone<T>(a, d, e, ds);
         a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
@@ -247,10 +277,20 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
     }
   }
   {
+    // worker threads (everyone when the CTA has no spare warps): herd centroid per env in float64, then the
+    // alpha-lattice term of the herds that update this step -- neither depends on the drones
     const int wt0 = (ndt < nt) ? ndt : 0;
     const int nw = nt - wt0;
     if (t >= wt0) {
-      for (int it = t - wt0; it < nact * M; it += nw) {
+      const int w = t - wt0;
+      if (w < G) {
+        double cx = 0, cy = 0;
+#pragma unroll 4
+        for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + w]; cx += (double)c.x; cy += (double)c.y; }
+        const double inv_m = 1.0 / (double)M;
+        s.ccent[w] = make_double2(cx * inv_m, cy * inv_m);
+      }
+      for (int it = w; it < nact * M; it += nw) {
         const int g = s.flist[it % nact], i = it / nact;
         T ux, uy;
         alpha_term<T>(s.cpos, s.cvel, i, g, G, M, ux, uy);
@@ -259,17 +299,26 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
     }
   }
   __syncthreads();
+  CHS_STAMP(2);
 
   // ---------------- phase 2 ----------------
+  // per-drone pieces: neighbour ranking + spacing rewards on the drone threads, cattle pieces on threads half a
+  // CTA away so that the two halves run on different warps
   if (t < ndt) {
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       const int n = s.n[g];
-      if (e < E && d < n) {
-        const int level = s.level[g];
-        drone_reduce<T>(p, g, d, n, level, true, s.dpos, s.cpos, s.redA, s.redB, s.stage,
-                        a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr);
-      }
+      if (e < E && d < n)
+        drone_neighbors<T>(p, g, d, n, s.level[g], true, s.dpos, s.redA, s.redB, s.stage,
+                           a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr);
+    }
+  }
+  {
+    const int half = (nt >> 1) & ~31;
+    const int tb = (t >= half) ? t - half : t + nt - half;
+    for (int it = tb; it < DG; it += nt) {
+      const int g = it & (G - 1), d = it >> lg, e = e0 + g;
+      if (e < E && d < s.n[g]) drone_cattle<T>(p, g, d, true, s.dpos, s.cpos, s.redB, s.stage);
     }
   }
   for (int it = t; it < nact * M; it += nt) {
@@ -287,6 +336,7 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
     }
   }
   __syncthreads();
+  CHS_STAMP(3);
 
   // ---------------- phase 3 ----------------
   if (t < 32) {
@@ -299,30 +349,28 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       double2 ef = pre_f;
       int level = ej.x;
       const int level_in = level;
-      // Per-env scalar arithmetic is float64 in both builds (one thread per env, ~100 flops): the approach term
-      // amplifies centroid-distance differences by 5*ctrl_freq/2.5 and the spacing clock counts in 1/240.
-      // sums in the reference's order: drone by drone, nearest neighbour first (CattleAviary.py:231-247)
-      double ssum = 0, csum = 0, c2d = 0, ms = Mth<double>::inf(), dcx = 0, dcy = 0;
+      // sums in the reference's order: drone by drone, nearest neighbour first (CattleAviary.py:231-247).
+      // The centroid distance, the approach term and the spacing clock are float64 in both builds: the approach
+      // term amplifies centroid-distance differences by 5*ctrl_freq/2.5 and the clock counts in 1/240.
+      T ssum = 0, csum = 0, c2d = 0, ms = Mth<T>::inf();
+      double dcx = 0, dcy = 0;
       bool alt_bad = false, isolated = false;
       for (int d = 0; d < n; ++d) {
         const auto A = s.redA[d * G + t];
         const auto B = s.redB[d * G + t];
         const auto P = s.dpos[d * G + t];
-        csum += (double)A.z; ssum += (double)A.x; csum += (double)A.w; ssum += (double)A.y;
-        c2d += (double)B.x;
-        ms = fmin(ms, (double)B.y);
+        csum += A.z; ssum += A.x; csum += A.w; ssum += A.y;
+        c2d += B.x;
+        ms = Mth<T>::min(ms, B.y);
         isolated = isolated || (B.y > T(k::MAX_FORMATION_DISTANCE));
         alt_bad = alt_bad || (B.z != T(0));
         dcx += (double)P.x; dcy += (double)P.y;
       }
-      const double inv_n = 1.0 / (double)n;
-      csum *= 0.5 * inv_n; ssum *= 0.5 * inv_n; c2d *= inv_n;
-      dcx *= inv_n; dcy *= inv_n;
-      double ccx = 0, ccy = 0;
-      for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + t]; ccx += (double)c.x; ccy += (double)c.y; }
-      const double inv_m = 1.0 / (double)M;
-      ccx *= inv_m; ccy *= inv_m;
-      const double ddx = dcx - ccx, ddy = dcy - ccy;
+      const double inv_n = c_inv_n[n];
+      const T inv_nT = T(inv_n);
+      csum *= T(0.5) * inv_nT; ssum *= T(0.5) * inv_nT; c2d *= inv_nT;
+      const double2 cc = s.ccent[t];
+      const double ddx = dcx * inv_n - cc.x, ddy = dcy * inv_n - cc.y;
       const double cent = sqrt(ddx * ddx + ddy * ddy + 0.0);
       double approach = 0;
       if (ef.x == ef.x) {   // prev_cent_dists is not None
@@ -332,11 +380,12 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       ef.x = cent;
       const int herded = s.herd[t];
       const double eff = (M > 0) ? (double)herded / (double)M * 100.0 : 0.0;
-      const double r_global = ssum * c_curr[level][k::C_W_SIMPLE] + csum * c_curr[level][k::C_W_COMPLEX] +
+      const double r_global = (double)ssum * c_curr[level][k::C_W_SIMPLE] + (double)csum * c_curr[level][k::C_W_COMPLEX] +
                               0.1 * c_curr[level][k::C_W_SURV] + approach * c_curr[level][k::C_W_APPROACH] +
-                              (eff / 100.0) * c_curr[level][k::C_W_EFF] + c2d * c_curr[level][k::C_W_C2D];
+                              (eff / 100.0) * c_curr[level][k::C_W_EFF] + (double)c2d * c_curr[level][k::C_W_C2D];
+      const double msd = (double)ms;
       // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
-      const bool term1 = compute_terminated<double>(level, ms, cent, eff, ef.y);
+      const bool term1 = compute_terminated<double>(level, msd, cent, eff, ef.y);
       if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
         ej.y += 1;
         if (ej.y >= (int)c_curr[level_in][k::C_REQ_TALLY]) {
@@ -346,11 +395,11 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       }
       ej.x = level;
       // second call, the one step() returns (BaseAviary.py:458)
-      const bool term = compute_terminated<double>(level, ms, cent, eff, ef.y);
+      const bool term = compute_terminated<double>(level, msd, cent, eff, ef.y);
       // _computeTruncated (:497-552), first hit in the reference's order
       int cause = -1;
       if (alt_bad) cause = 0;
-      else if (ms < k::COLLISION_THRESHOLD) cause = 1;
+      else if (msd < k::COLLISION_THRESHOLD) cause = 1;
       else if (isolated) cause = 2;
       else if (cent > k::MISSION_BOUNDARY) cause = 3;
       else if (ei.x > p.trunc_step_limit) cause = 4;
@@ -393,6 +442,7 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
     if (t == 0) { s.misc[1] = __popc(m); if (blockIdx.x == 0) atomicAdd(a.stats + 10, (double)E); }
   }
   __syncthreads();
+  CHS_STAMP(4);
 
   // ---------------- phase 4 ----------------
   const int nd = s.misc[1];
@@ -410,10 +460,13 @@ __global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
       if (dst) copy_rows(p, s.stage + (size_t)g * p.stage_stride, dst, lane);
     }
   }
+  CHS_STAMP(5);
   // ---------------- phase 5 ----------------
   if (nd > 0) {
     reset_envs<T>(a, s, e0, nd);
   }
+  CHS_STAMP(6);
+#undef CHS_STAMP
 }
 
 }  // namespace chs

@@ -63,11 +63,12 @@ template <typename T> struct KArgs {
   const uint8_t* reset_mask;         // reset kernel only (nullable = all)
   int* dbg_neighbors;                // nullable [E][D][2]
   int* dbg_herded;                   // nullable [E]
+  long long* dbg_clock;              // nullable [grid][8]: clock64() of thread 0 at each phase boundary
 };
 
 // ---- shared-memory carve-up (per CTA of G envs) ----------------------------------------------------
 struct SmemLayout {
-  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_int, total;
+  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_ccent, off_int, total;
 };
 
 template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, int M, int G, int stage_stride) {
@@ -82,6 +83,7 @@ template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, i
   s.off_u = o;    o += M * G * v2;
   o = (o + 15) & ~15;
   s.off_stage = o; o += G * stage_stride * 4;
+  s.off_ccent = o; o += G * 16;
   s.off_int = o;  o += (10 * 32 + 8) * 4;  // ten per-env int arrays [32] + misc
   s.total = o;
   return s;

@@ -7,6 +7,10 @@ namespace chs {
 
 __constant__ double c_curr[k::NUM_LEVELS][k::C_NCOLS] = {CHS_CURRICULUM_ROWS};
 
+// 1/n for n = 0..12 drones (n = 0 never divides)
+__constant__ double c_inv_n[CHS_MAX_DRONES + 1] = {0.0, 1.0, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7,
+                                                   1.0 / 8, 1.0 / 9, 1.0 / 10, 1.0 / 11, 1.0 / 12};
+
 template <typename T> __device__ __forceinline__ T curr(int level, int col) { return T(c_curr[level][col]); }
 
 // CattleAviary.SimpleSpacingReward (:594-626)
@@ -42,19 +46,19 @@ template <typename T> __device__ __forceinline__ T cattle_spacing(T r) {
 // Per-drone results handed from the (env, drone) threads to the per-env combine through shared memory.
 //   redA = (simple(d1), simple(d2), complex(d1), complex(d2))
 //   redB = (cattle_spacing(min cow distance), d1 = distance to the nearest other drone, altitude-violation flag, 0)
+// The obs row (BaseRLAviary.py:286-334) is [z rpy vel ang_v | rel-xy of the 2 nearest drones, stable order |
+// zeros up to 12 neighbour slots | rel-xy of cows 0..15 | zeros]; the own-state part is written by the thread
+// that integrated the drone, the neighbour part by drone_neighbors, the cattle part by drone_cattle.  The two
+// functions touch disjoint shared-memory words, so different threads may run them concurrently.
 
-// Everything one drone contributes to the observation row and to the reward/flag reductions.
-//   obs row (BaseRLAviary.py:286-334): [z rpy vel ang_v | rel-xy of the 2 nearest drones, stable order |
-//   zeros up to 12 neighbour slots | rel-xy of cows 0..15 | zeros]; only the neighbour and cattle parts are
-//   written here (the own-state part is written by the thread that integrated the drone).
 template <typename T>
-__device__ __forceinline__ void drone_reduce(const KParams& p, int g, int d, int n, int level, bool want_reward,
-                                             const typename VT<T>::v4* s_dpos, const typename VT<T>::v2* s_cpos,
-                                             typename VT<T>::v4* s_redA, typename VT<T>::v4* s_redB,
-                                             float* s_stage, int* dbg_nb /* nullable: [2] */) {
+__device__ __forceinline__ void drone_neighbors(const KParams& p, int g, int d, int n, int level, bool want_reward,
+                                                const typename VT<T>::v4* s_dpos, typename VT<T>::v4* s_redA,
+                                                typename VT<T>::v4* s_redB, float* s_stage, int* dbg_nb /* nullable: [2] */) {
   const int G = p.G;
   const auto me = s_dpos[d * G + g];
-  // two nearest other drones; strict '<' keeps index order on ties (stable sort, :310-311)
+  // two nearest other drones; strict '<' keeps index order on ties (stable sort, :310-311);
+  // a NaN distance never wins '<', and numpy's stable argsort puts NaN last as well
   T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
   int j1 = -1, j2 = -1;
   for (int j = 0; j < n; ++j) {
@@ -65,7 +69,6 @@ __device__ __forceinline__ void drone_reduce(const KParams& p, int g, int d, int
     if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
     else if (dist < d2) { d2 = dist; j2 = j; }
   }
-  // a NaN distance never wins '<'; numpy's stable argsort puts NaN last as well
   float* row = s_stage + (size_t)g * p.stage_stride + d * p.L;
   const int nb_slots = (p.L - 10) / 2;       // row truncated to L (BaseRLAviary.py:336-340)
   if (j1 >= 0 && nb_slots > 0) {
@@ -77,25 +80,44 @@ __device__ __forceinline__ void drone_reduce(const KParams& p, int g, int d, int
     row[12] = (float)(o.x - me.x); row[13] = (float)(o.y - me.y);
   }
   if (dbg_nb) { dbg_nb[0] = j1; dbg_nb[1] = j2; }
-  // cattle: relative xy of cows 0..15 into the row, minimum distance over ALL cows for the reward
-  T m2 = Mth<T>::inf();
-  const int cbase = 10 + 2 * CHS_MAX_DRONES;   // neighbours are padded to 12 slots, not 4 (:313-314)
-  for (int j = 0; j < p.M; ++j) {
-    const auto c = s_cpos[j * G + g];
-    const T dx = c.x - me.x, dy = c.y - me.y;
-    if (j < 16) {
-      const int col = cbase + 2 * j;
-      if (col + 1 < p.L) { row[col] = (float)dx; row[col + 1] = (float)dy; }
-      else if (col < p.L) { row[col] = (float)dx; }
-    }
-    m2 = Mth<T>::min(m2, dx * dx + dy * dy);
-  }
   if (want_reward) {
     const T desired = curr<T>(level, k::C_DESIRED), tolf = curr<T>(level, k::C_TOL);
     s_redA[d * G + g] = mk4<T>(simple_spacing<T>(d1, desired, tolf), simple_spacing<T>(d2, desired, tolf),
                                complex_spacing<T>(d1, desired), complex_spacing<T>(d2, desired));
-    const T alt_bad = (Mth<T>::abs(me.z - T(k::TARGET_ALT)) > T(k::MAX_ALT_ERROR)) ? T(1) : T(0);
-    s_redB[d * G + g] = mk4<T>(cattle_spacing<T>(Mth<T>::sqrt(m2)), d1, alt_bad, T(0));
+    T* rb = reinterpret_cast<T*>(&s_redB[d * G + g]);
+    rb[1] = d1;
+    rb[2] = (Mth<T>::abs(me.z - T(k::TARGET_ALT)) > T(k::MAX_ALT_ERROR)) ? T(1) : T(0);
+  }
+}
+
+// cattle: relative xy of cows 0..15 into the obs row, minimum distance over ALL cows for the reward
+template <typename T>
+__device__ __forceinline__ void drone_cattle(const KParams& p, int g, int d, bool want_reward,
+                                             const typename VT<T>::v4* s_dpos, const typename VT<T>::v2* s_cpos,
+                                             typename VT<T>::v4* s_redB, float* s_stage) {
+  const int G = p.G;
+  const auto me = s_dpos[d * G + g];
+  float* row = s_stage + (size_t)g * p.stage_stride + d * p.L;
+  T m2 = Mth<T>::inf();
+  const int cbase = 10 + 2 * CHS_MAX_DRONES;   // neighbours are padded to 12 slots, not 4 (:313-314)
+  const int nobs = (p.M < 16) ? p.M : 16;
+#pragma unroll 4
+  for (int j = 0; j < nobs; ++j) {
+    const auto c = s_cpos[j * G + g];
+    const T dx = c.x - me.x, dy = c.y - me.y;
+    const int col = cbase + 2 * j;
+    if (col + 1 < p.L) { row[col] = (float)dx; row[col + 1] = (float)dy; }
+    else if (col < p.L) { row[col] = (float)dx; }
+    m2 = Mth<T>::min(m2, dx * dx + dy * dy);
+  }
+  if (want_reward) {
+#pragma unroll 4
+    for (int j = nobs; j < p.M; ++j) {
+      const auto c = s_cpos[j * G + g];
+      const T dx = c.x - me.x, dy = c.y - me.y;
+      m2 = Mth<T>::min(m2, dx * dx + dy * dy);
+    }
+    reinterpret_cast<T*>(&s_redB[d * G + g])[0] = cattle_spacing<T>(Mth<T>::sqrt(m2));
   }
 }
 

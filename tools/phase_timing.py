@@ -1,0 +1,43 @@
+"""Per-phase latency of the fused step kernel from in-kernel clock64() stamps (GPU box).
+    python tools/phase_timing.py [envs] [G] [threads]"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path.insert(0, ROOT)
+import rl_cattle_herding_b200 as pkg  # noqa: E402
+
+E = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+G = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+TH = int(sys.argv[3]) if len(sys.argv) > 3 else 128
+N, M = 3, 20
+env = pkg.CattleHerdingBatchedEnv(E, num_drones=N, num_cattle=M, fixed_num_drones=N, spawn_table=pkg.spawn.generate(100, M),
+                                  device=0, envs_per_block=G, threads_per_block=TH)
+env.reset()
+grid = (E + G - 1) // G
+clk = torch.zeros((grid, 8), dtype=torch.int64, device="cuda")
+acts = [torch.rand((E, N, 4), device="cuda") * 2 - 1 for _ in range(8)]
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+for i in range(40):
+    env.step(acts[i % 8])
+pkg._lib.check(env.lib.chs_set_phase_clock(env._h, C.c_void_p(clk.data_ptr())))
+acc = np.zeros(6)
+tot = 0.0
+R = 20
+for i in range(R):
+    flush.zero_()
+    env.step(acts[i % 8])
+    torch.cuda.synchronize()
+    c = clk.cpu().numpy().astype(np.float64)
+    d = np.diff(c[:, :7], axis=1)
+    acc += d.mean(axis=0)
+    tot += (c[:, 6].max() - c[:, 0].min())
+names = ["p0 load", "p1 drone|alpha", "p2 reduce|finish", "p3 per-env", "p4 copy-out", "p5 reset"]
+print(f"E={E} G={G} threads={TH} grid={grid}: mean cycles per phase (avg over CTAs, {R} steps)")
+for n, v in zip(names, acc / R):
+    print(f"  {n:18s} {v:9.0f} cyc")
+print(f"  sum {acc.sum() / R:.0f} cyc; kernel span (max end - min start over CTAs) {tot / R:.0f} cyc")
