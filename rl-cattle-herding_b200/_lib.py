@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libchs.so")
+LIB_PATH = os.environ.get("CHS_LIB", os.path.join(_HERE, "libchs.so"))   # CHS_LIB: build-variant experiments
 
 ABI_VERSION = 1
 MAX_DRONES = 12

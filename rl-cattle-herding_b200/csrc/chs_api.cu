@@ -43,6 +43,7 @@ struct ChsHandle {
   int *dbg_nb, *dbg_herd;
   long long* dbg_clock;
   int threads, smem;
+  int reg_variant;            // 0 auto, 1 latency (128 regs), 2 occupancy (64 regs)
   bool spawn_set;
   // device-side buffers of the host path (allocated on first use)
   float *d_actions, *d_obs, *d_reward, *d_termobs;
@@ -84,10 +85,11 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
   if (smem > 200 * 1024) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
   DeviceGuard dg(h->device);
   if (h->f64) {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     CUDA_TRY(cudaFuncSetAttribute(reset_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   } else {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     CUDA_TRY(cudaFuncSetAttribute(reset_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   }
   h->kp.G = G;
@@ -294,6 +296,17 @@ extern "C" int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_d
                 : launch_reset<float>(h, env_mask_dev, obs_dev, (cudaStream_t)stream);
 }
 
+template <typename T> static void launch_step_variant(ChsHandle* h, const KArgs<T>& a, int grid, cudaStream_t st);
+template <> void launch_step_variant<double>(ChsHandle* h, const KArgs<double>& a, int grid, cudaStream_t st) {
+  step_kernel<double, 512, 1><<<grid, h->threads, h->smem, st>>>(a);
+}
+template <> void launch_step_variant<float>(ChsHandle* h, const KArgs<float>& a, int grid, cudaStream_t st) {
+  // latency variant while the grid is under ~512 threads per SM, occupancy variant beyond
+  const bool big = h->reg_variant == 2 || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
+  if (big) step_kernel<float, 256, 4><<<grid, h->threads, h->smem, st>>>(a);
+  else step_kernel<float, 512, 1><<<grid, h->threads, h->smem, st>>>(a);
+}
+
 template <typename T>
 static int launch_step(ChsHandle* h, const float* actions, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
                        float* term_obs, int term_mode, int* term_count, int* term_idx, cudaStream_t st) {
@@ -301,7 +314,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   a.actions = actions; a.obs = obs; a.reward = reward; a.terminated = term; a.truncated = trunc;
   a.term_obs = term_obs; a.term_mode = term_obs ? term_mode : 0; a.term_count = term_count; a.term_idx = term_idx;
   const int grid = (h->E + h->kp.G - 1) / h->kp.G;
-  step_kernel<T><<<grid, h->threads, h->smem, st>>>(a);
+  launch_step_variant<T>(h, a, grid, st);
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;
 }

@@ -183,8 +183,11 @@ __global__ void __launch_bounds__(512) reset_kernel(const KArgs<T> a) {
   if (nd > 0) reset_envs<T>(a, s, e0, nd);
 }
 
-template <typename T>
-__global__ void __launch_bounds__(512) step_kernel(const KArgs<T> a) {
+// Two register budgets are compiled: MINB = 1 (up to 128 registers per thread, shortest dependent chains, for
+// grids of about one wave where latency decides) and MINB = 4 (64 registers, 4 CTAs of 256 threads per SM, for
+// large batches where issue-slot occupancy decides).  The host picks by grid size.
+template <typename T, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const KParams& p = a.p;
   Smem<T> s = carve<T>(smem_raw, p);
