@@ -170,6 +170,11 @@ int chs_set_state(ChsHandle* h, int32_t env0, int32_t count, const ChsStateView*
  * int32 [E].  Pass NULL to disable. */
 int chs_set_debug_buffers(ChsHandle* h, int32_t* neighbors_dev, int32_t* herded_dev);
 
+/* The fp32 step kernel is compiled with two register budgets: 1 = latency (<=128 registers/thread, for grids of
+ * about one wave), 2 = occupancy (64 registers, 4 CTAs of 256 threads per SM, for large batches); 0 = chosen
+ * by grid size at every launch (default). */
+int chs_set_register_variant(ChsHandle* h, int32_t variant);
+
 /* Profiling aid: when non-NULL, thread 0 of every CTA of chs_step writes clock64() at the 7 phase boundaries
  * of the fused kernel into int64 [grid][8] (grid = ceil(E / envs_per_block)).  NULL disables. */
 int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev);

@@ -18,7 +18,7 @@ STAT_NAMES = ("episodes", "sum_return", "sum_length", "terminated", "trunc_altit
 # every symbol include/chs.h declares (checked by tests/test_abi.py)
 SYMBOLS = ("chs_abi_version", "chs_last_error", "chs_create", "chs_destroy", "chs_get_dims", "chs_set_spawn_table",
            "chs_reset", "chs_step", "chs_step_host", "chs_reset_host", "chs_get_state", "chs_set_state",
-           "chs_set_debug_buffers", "chs_set_phase_clock", "chs_stats", "chs_set_launch")
+           "chs_set_debug_buffers", "chs_set_phase_clock", "chs_set_register_variant", "chs_stats", "chs_set_launch")
 
 
 class ChsParams(C.Structure):
@@ -75,6 +75,7 @@ def load():
     lib.chs_set_state.argtypes = [vp, i32, i32, C.POINTER(ChsStateView)]
     lib.chs_set_debug_buffers.argtypes = [vp, vp, vp]
     lib.chs_set_phase_clock.argtypes = [vp, vp]
+    lib.chs_set_register_variant.argtypes = [vp, i32]
     lib.chs_stats.argtypes = [vp, vp, i32]
     lib.chs_set_launch.argtypes = [vp, i32, i32]
     for s in SYMBOLS:

@@ -78,19 +78,23 @@ static int smem_for(const ChsHandle* h, int G) {
   return h->f64 ? layout_for<double>(h->kp, G).total : layout_for<float>(h->kp, G).total;
 }
 
+static const int kSmemCap = 200 * 1024;
+
 static int configure_launch(ChsHandle* h, int G, int threads) {
   if (G < 1 || G > 32 || (G & (G - 1))) return fail(CHS_ERR_INVALID, "envs_per_block must be a power of two in 1..32");
   if (threads < 32 || threads > 512 || (threads & 31)) return fail(CHS_ERR_INVALID, "threads_per_block must be a multiple of 32 in 32..512");
   const int smem = smem_for(h, G);
-  if (smem > 200 * 1024) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
+  // the opt-in limit is a per-function, process-wide attribute: always raise it to the cap so that handles with
+  // different shared-memory needs can coexist (the launch's own size decides occupancy)
+  if (smem > kSmemCap) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
   DeviceGuard dg(h->device);
   if (h->f64) {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
   } else {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
   }
   h->kp.G = G;
   h->threads = threads;
@@ -251,6 +255,14 @@ extern "C" int chs_set_spawn_table(ChsHandle* h, const double* xy, int32_t n_sim
   return CHS_OK;
 }
 
+extern "C" int chs_set_register_variant(ChsHandle* h, int32_t variant) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  if (variant < 0 || variant > 2) return fail(CHS_ERR_INVALID, "variant must be 0 (auto), 1 (latency) or 2 (occupancy)");
+  if (variant == 2 && h->threads > 256) return fail(CHS_ERR_INVALID, "the occupancy variant needs threads_per_block <= 256");
+  h->reg_variant = variant;
+  return CHS_OK;
+}
+
 extern "C" int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev) {
   if (!h) return fail(CHS_ERR_INVALID, "null handle");
   h->dbg_clock = (long long*)clock_dev;
@@ -302,7 +314,7 @@ template <> void launch_step_variant<double>(ChsHandle* h, const KArgs<double>& 
 }
 template <> void launch_step_variant<float>(ChsHandle* h, const KArgs<float>& a, int grid, cudaStream_t st) {
   // latency variant while the grid is under ~512 threads per SM, occupancy variant beyond
-  const bool big = h->reg_variant == 2 || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
+  const bool big = (h->reg_variant == 2 && h->threads <= 256) || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
   if (big) step_kernel<float, 256, 4><<<grid, h->threads, h->smem, st>>>(a);
   else step_kernel<float, 512, 1><<<grid, h->threads, h->smem, st>>>(a);
 }
