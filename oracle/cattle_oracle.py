@@ -715,6 +715,173 @@ class OracleEnv:
         return float(np.mean(per_drone))
 
     # ---------------------------------------------------------------------------------------------
+    # MARL packing  (rllib_envs/BaseMARLAviary.py:253-303, MARLCattleAviary.py:110-383,
+    #                rllib_envs/BaseAviary.py:320-438)
+    # ---------------------------------------------------------------------------------------------
+    def compute_obs_marl(self, i):
+        """Per-drone observation (L,): neighbours are padded to MAX_NEIGHBORS = 4 here, so there is no dead gap."""
+        n, L = self.n_drones, self.L
+        row = [self.pos[i][2], *self.rpy[i], *self.vel[i], *self.ang_v[i]]
+        rel = []
+        for j in range(n):
+            if j == i:
+                continue
+            d = self.pos[j][:2] - self.pos[i][:2]
+            rel.append((d, math.sqrt(d[0] ** 2 + d[1] ** 2), j))
+        rel.sort(key=lambda t: t[1])
+        rel = rel[:ACTIVE_NEIGHBORS]
+        nb = [t[0] for t in rel]
+        while len(nb) < MAX_NEIGHBORS:
+            nb.append(np.zeros(2))
+        for v in nb:
+            row.extend(v)
+        cat = [self.cattle_pos[j][:2] - self.pos[i][:2] for j in range(self.M)]
+        while len(cat) < MAX_NEARBY_CATTLE:
+            cat.append(np.zeros(2))
+        for v in cat[:MAX_NEARBY_CATTLE]:
+            row.extend(v)
+        row.extend([0.0] * (self.ABS * self.ACTION_SPACE))     # reset-time zeros, never refreshed (:305,294)
+        arr = np.array(row, dtype=np.float32)
+        return arr[:L] if len(arr) >= L else np.pad(arr, (0, L - len(arr)))
+
+    def compute_terminated_marl(self):
+        """MARLCattleAviary._computeTerminated (:246-321): drone independent, clock += 1/CTRL_FREQ per CALL."""
+        row = self._row()
+        lvl = self.level
+        if lvl in (0, 1):
+            desired, tol = row[C_DESIRED], row[C_TOL]
+            hi, lo = desired + desired * tol, desired - desired * tol
+            ms = self._min_spacing()
+            if lo < ms < hi:
+                self.spacing_clock += 1 / self.CTRL_FREQ
+                if self.spacing_clock >= row[C_HOLD]:
+                    return True
+            else:
+                self.spacing_clock = 0
+        elif lvl in (2, 3):
+            if self._centroid_dist() < row[C_APPROACH_MIN]:
+                return True
+        elif lvl in (4, 6):
+            if self.effectiveness() > row[C_MIN_EFF]:
+                return True
+        elif lvl == 5:
+            if self.effectiveness() > row[C_MIN_EFF]:
+                desired, tol = row[C_CATTLE_DESIRED], row[C_CATTLE_TOL]
+                hi, lo = desired + desired * tol, desired - desired * tol
+                if lo < self._min_spacing() < hi:
+                    return True
+        return False
+
+    def compute_truncated_marl(self, i):
+        """MARLCattleAviary._computeTruncated (:326-383): own altitude / collision / isolation, shared rest."""
+        n = self.n_drones
+        cent = self._centroid_dist()
+        if abs(self.pos[i][2] - TARGET_ALT) > MAX_ALT_ERROR:
+            return True
+        xy = self.pos[:n, :2]
+        for j in range(n):
+            if j != i:
+                d = xy[i] - xy[j]
+                if math.sqrt(d[0] ** 2 + d[1] ** 2) < COLLISION_THRESHOLD:
+                    return True
+        d = np.sqrt(np.sum((xy - xy[i]) ** 2, axis=1))
+        d[i] = np.inf
+        if np.all(d > MAX_FORMATION_DISTANCE):
+            return True
+        if cent > MISSION_BOUNDARY:
+            return True
+        if self.step_counter / self.CTRL_FREQ > self.EPISODE_LEN_SEC:
+            return True
+        return False
+
+    def _end_of_episode_marl(self, i):
+        """MARLCattleAviary._endOfEpisodeReward (:180-241)."""
+        n = self.n_drones
+        row = self._row()
+        lvl = self.level
+        r = 0.0
+        if lvl in (0, 1):
+            desired, tol = row[C_DESIRED], row[C_TOL]
+            hi, lo = desired + desired * tol, desired - desired * tol
+            two = self._two_nearest(i)
+            if np.all((two >= lo) & (two <= hi)):
+                r += 50.0 / n
+        elif lvl in (2, 3):
+            if self._centroid_dist() < row[C_APPROACH_MIN]:
+                r += 50.0
+        elif lvl in (4, 6):
+            eff = self.effectiveness()
+            cc = np.mean(self.cattle_pos[:, :2], axis=0)
+            dd = cc - self.pos[i, :2]
+            w = min(max(1.0 - math.sqrt(dd[0] ** 2 + dd[1] ** 2) / 10.0, 0.0), 1.0)
+            r += eff * 2 * w
+        elif lvl == 5:
+            if self.effectiveness() > row[C_MIN_EFF]:
+                desired, tol = row[C_CATTLE_DESIRED], row[C_CATTLE_TOL]
+                hi, lo = desired + desired * tol, desired - desired * tol
+                two = self._two_nearest(i)
+                if np.all((two >= lo) & (two <= hi)):
+                    r += 50.0 / n
+        return r
+
+    def compute_reward_marl(self, i):
+        """MARLCattleAviary._computeReward (:110-178).  Stateful: prev_cent_dist (so only the first drone of a
+        step sees a non-zero approach term), the spacing clock and the curriculum tally/level."""
+        two = self._two_nearest(i)
+        s_simple = (self.simple_spacing(float(two[0])) + self.simple_spacing(float(two[1]))) / 2
+        s_complex = (self.complex_spacing(float(two[0])) + self.complex_spacing(float(two[1]))) / 2
+        r = 0.0
+        r += s_simple * self._row()[C_W_SIMPLE]
+        r += s_complex * self._row()[C_W_COMPLEX]
+        r += 0.1 * self._row()[C_W_SURV]
+        cent = self._centroid_dist()
+        change = 0.0 if math.isnan(self.prev_cent_dist) else self.prev_cent_dist - cent
+        self.prev_cent_dist = cent
+        r += _clip((change / (SPEED_LIMIT / self.CTRL_FREQ + 1e-6)) * 5, -1.0, 1.0) * self._row()[C_W_APPROACH]
+        r += (self.effectiveness() / 100) * self._row()[C_W_EFF]
+        dmin = float(np.min(np.sqrt(np.sum((self.cattle_pos[:, :2] - self.pos[i, :2]) ** 2, axis=1))))
+        r += self.cattle_spacing(dmin) * self._row()[C_W_C2D]
+        if self.compute_terminated_marl():
+            r += self._end_of_episode_marl(i)
+            row = self._row()
+            self.tally += 1
+            if self.tally >= row[C_REQ_TALLY]:
+                self.tally = 0
+                self.level = min(self.level + 1, len(CURRICULUM) - 1)
+        elif self.compute_truncated_marl(i):
+            r -= 50
+        return float(r)
+
+    def step_marl(self, action):
+        """rllib_envs/BaseAviary.step (:320-438): per-drone outputs, `step_counter += 1`.
+        Returns (obs (12, L) f32, reward (12,), terminated (12,) bool, truncated (12,) bool)."""
+        self.step_counter_A += 1
+        n = self.n_drones
+        rpm = self.preprocess_action(np.asarray(action))
+        for _ in range(self.K):
+            for k in range(n):
+                self._dynamics(k, rpm[k])
+            self.last_rpm[:n] = rpm
+        for k in range(n):
+            self.rpy[k] = quat_to_euler(tuple(self.quat[k]))
+        if self.step_counter_A % 2 == 0:
+            self.flocking_step()
+        obs = np.zeros((NMAX, self.L), dtype=np.float32)
+        rew = np.zeros(NMAX)
+        term = np.zeros(NMAX, dtype=bool)
+        trunc = np.zeros(NMAX, dtype=bool)
+        for i in range(n):
+            obs[i] = self.compute_obs_marl(i)
+        for i in range(n):
+            rew[i] = self.compute_reward_marl(i)
+        for i in range(n):
+            term[i] = self.compute_terminated_marl()
+        for i in range(n):
+            trunc[i] = self.compute_truncated_marl(i)
+        self.step_counter += 1
+        return obs, rew, term, trunc
+
+    # ---------------------------------------------------------------------------------------------
     # step  (BaseAviary.py:335-465)
     # ---------------------------------------------------------------------------------------------
     def step(self, action):

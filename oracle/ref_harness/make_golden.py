@@ -228,6 +228,59 @@ def act_one_d_pid():
     _act_run("act_one_d_pid", "one_d_pid", 1)
 
 
+# ---- MARL (rllib_envs) fixtures ------------------------------------------------------------------------
+def _marl_run(name, level, n, m, steps, prep=None, tally=None, clock=None, zero=False, gentle=True, table=None, seed=71):
+    table = ref_env.shipped_spawn_table() if table is None else table
+    env = ref_env.make_reference_marl_env(n, m, ctrl_freq=30, level=level, seed=seed + level,
+                                          spawn_table=None if m <= 16 and table.shape[1] == 16 else table)
+    ref_env.quiet(env.reset)
+    if prep is not None:
+        prep(env)
+    if tally is not None:
+        env.curriculum.curriculum_success_tally = tally
+    if clock is not None:
+        env.drone_spacing_clock = clock
+    acts = zero_actions(steps) if zero else (gentle_actions(73 + level, steps) if gentle else uniform_actions(79 + level, steps))
+    rec = ref_env.record_marl_rollout(env, acts, reset_first=False)
+    _finish(name, env, rec, dict(n_drones=n, start_level=level, act="vel", packing="marl"), table)
+
+
+@scenario
+def m_3d20c_uniform():
+    """MARL packing, the reference's default level 0 (3 drones), BASELINE shape, uniform actions."""
+    table = ref_env.synthetic_spawn_table(100, 20, seed=0)
+    _marl_run("m_3d20c_uniform", 0, 3, 20, 120, gentle=False, table=table)
+
+
+@scenario
+def m_l0_hold_levelup():
+    """Level 0: spacing clock just below the hold timer and tally just below the threshold: the 2N
+    _computeTerminated calls of one step cross the timer, per-drone end-of-episode rewards fire and the level
+    bumps in the middle of the per-drone reward loop."""
+    _marl_run("m_l0_hold_levelup", 0, 3, 16, 20, prep=lambda e: teleport_drones(e, [(0, 0), (0.8, 0), (1.6, 0)]),
+              tally=98, clock=10 - 3.5 / 30, zero=True)
+
+
+@scenario
+def m_l2_approach():
+    _marl_run("m_l2_approach", 2, 4, 16, 30, prep=lambda e: teleport_drones(e, ring_around_herd(e, 1.3, 0.2)), tally=97)
+
+
+@scenario
+def m_l4_surround():
+    _marl_run("m_l4_surround", 4, 4, 16, 30, prep=lambda e: teleport_drones(e, ring_around_herd(e, 2.2, 0.4)))
+
+
+@scenario
+def m_l5_surround_spacing():
+    _marl_run("m_l5_surround_spacing", 5, 4, 1, 20, prep=lambda e: teleport_drones(e, ring_around_herd(e, 0.58, 0.1)), zero=True)
+
+
+@scenario
+def m_l7_6d():
+    _marl_run("m_l7_6d", 7, 6, 16, 60, gentle=False)
+
+
 if __name__ == "__main__":
     names = sys.argv[1:] or list(SCENARIOS)
     for nm in names:

@@ -211,3 +211,73 @@ def record_rollout(env, actions, reset_first=True):
             quiet(env.reset)
         rows.append(row)
     return {k: np.stack([r[k] for r in rows]) for k in rows[0]}
+
+
+# ---- MARL (rllib_envs) variant -----------------------------------------------------------------------
+def import_reference_marl():
+    """Returns (MARLCattleAviary, Physics, ActionType, module) of the reference's rllib_envs stack."""
+    _ensure_paths()
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        with contextlib.redirect_stdout(io.StringIO()):
+            import gym_pybullet_drones.rllib_envs.MARLCattleAviary as m_mod
+            from gym_pybullet_drones.utils.enums import Physics, ActionType
+    return m_mod.MARLCattleAviary, Physics, ActionType, m_mod
+
+
+def make_reference_marl_env(n_drones, n_cattle, ctrl_freq=30, pyb_freq=240, level=0, seed=0, spawn_table=None):
+    """Constructs the reference `MARLCattleAviary` (rllib_envs/MARLCattleAviary.py) under Physics.DYN."""
+    MARL, Physics, ActionType, m_mod = import_reference_marl()
+    import yaml
+    random.seed(seed)
+    np.random.seed(seed)
+    orig_load = yaml.safe_load
+    orig_cl = m_mod.CurriculumLearning
+    if spawn_table is not None:
+        d = table_to_yaml_dict(np.asarray(spawn_table))
+        yaml.safe_load = lambda f: d
+    if level != 0:
+        m_mod.CurriculumLearning = lambda _lvl: orig_cl(level)
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            env = MARL(num_drones=12, num_cattle=n_cattle, physics=Physics.DYN, pyb_freq=pyb_freq, ctrl_freq=ctrl_freq,
+                       act=ActionType.VEL)
+    finally:
+        yaml.safe_load = orig_load
+        m_mod.CurriculumLearning = orig_cl
+    env.MIN_NUM_DRONES = env.MAX_NUM_DRONES = n_drones
+    return env
+
+
+def record_marl_rollout(env, actions, reset_first=True):
+    """Like record_rollout for the per-drone dict API (rllib_envs/BaseAviary.py:320-438): obs (12, L), reward,
+    terminated and truncated are (12,) arrays padded with zeros beyond NUM_DRONES.  An episode is restarted when
+    every drone is terminated or every drone is truncated (`__all__`), or when any flag is set (what a
+    VecEnv-style caller does) -- `reset_after` records which."""
+    if reset_first:
+        quiet(env.reset)
+    rows = []
+    for t in range(actions.shape[0]):
+        before = capture_state(env)
+        n = env.NUM_DRONES
+        a = actions[t].astype(np.float32)
+        obs, rew, term, trunc, _ = quiet(env.step, a[: max(n, 1)])
+        after = capture_state(env)
+        L = len(obs[0])
+        O = np.zeros((NMAX, L), dtype=np.float32)
+        R = np.zeros((NMAX,), dtype=np.float64)
+        T = np.zeros((NMAX,), dtype=np.uint8)
+        U = np.zeros((NMAX,), dtype=np.uint8)
+        for i in range(n):
+            O[i], R[i], T[i], U[i] = obs[i], rew[i], bool(term[i]), bool(trunc[i])
+        row = {"action": a, "obs": O, "reward": R, "terminated": T, "truncated": U,
+               "term_all": np.uint8(bool(term["__all__"])), "trunc_all": np.uint8(bool(trunc["__all__"]))}
+        row.update({"before_" + k: v for k, v in before.items()})
+        row.update({"after_" + k: v for k, v in after.items()})
+        done = bool(T[:n].any() or U[:n].any())
+        row["reset_after"] = np.uint8(done)
+        if done:
+            quiet(env.reset)
+        rows.append(row)
+    return {k: np.stack([r[k] for r in rows]) for k in rows[0]}

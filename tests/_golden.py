@@ -22,8 +22,11 @@ FLOAT_STATE = ("pos", "quat", "rpy", "vel", "ang_v", "rpy_rates", "last_rpm", "p
 INT_STATE = ("n_drones", "step_counter", "step_counter_A", "level", "tally", "spawn_idx")
 
 
-def golden_names():
-    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+def golden_names(packing="ctde"):
+    """Fixture names for one packing: `m_*` files hold MARL (rllib_envs) rollouts, the rest CTDE (sb3_envs)."""
+    names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+    marl = [n for n in names if n.startswith("m_")]
+    return marl if packing == "marl" else [n for n in names if n not in marl]
 
 
 class Golden:

@@ -61,3 +61,32 @@ def test_free_running_episodes(name):
             start = t + 1
             checked += 1
     assert checked >= 1
+
+
+@pytest.mark.parametrize("name", golden_names("marl"))
+def test_marl_teacher_forced(name):
+    """MARL packing (rllib_envs): per-drone obs / reward / flags, the sequential reward loop with its
+    mid-step curriculum bumps, clock += 1/CTRL_FREQ per call, control-step counter."""
+    g = Golden(name)
+    assert g.meta["packing"] == "marl"
+    env = g.make_oracle()
+    n_term = n_trunc = 0
+    for t in range(g.steps):
+        env.set_state(g.state(t, "before"))
+        obs, rew, term, trunc = env.step_marl(g.action(t))
+        after = g.state(t, "after")
+        got = env.get_state()
+        for k in INT_STATE:
+            assert int(got[k]) == int(after[k]), (name, t, k, got[k], after[k])
+        assert np.array_equal(term, g.z["terminated"][t]), (name, t, "terminated")
+        assert np.array_equal(trunc, g.z["truncated"][t]), (name, t, "truncated")
+        for k in FLOAT_STATE:
+            e = max_err(got[k], after[k])
+            scale = max(1.0, float(np.nanmax(np.abs(np.where(np.isfinite(after[k]), after[k], 0.0)))))
+            assert e <= TOL * scale, (name, t, k, e)
+        ref_obs = g.z["obs"][t]
+        assert obs.shape == ref_obs.shape and obs.dtype == np.float32
+        assert max_err(obs, ref_obs) <= 2e-7 * max(1.0, float(np.max(np.abs(ref_obs)))), (name, t, "obs")
+        assert max_err(rew, g.z["reward"][t]) <= TOL * max(1.0, float(np.max(np.abs(g.z["reward"][t])))), (name, t, "reward")
+        n_term += int(term.any()); n_trunc += int(trunc.any())
+    assert n_term + n_trunc >= 1
