@@ -22,6 +22,13 @@
  *   reward      float32 [E]         (CTDE packing, CattleAviary.py:332)
  *   terminated  uint8   [E]         (CattleAviary.py:422)
  *   truncated   uint8   [E]         (CattleAviary.py:497)
+ * MARL packing (rllib_envs/BaseAviary.py:425-430, the per-agent dicts as arrays; slots >= the env's
+ * drone count are zero):
+ *   obs         float32 [E][R][L]   row i = _computeObs(i) (rllib_envs/BaseMARLAviary.py:253-303), R = D
+ *   reward      float32 [E][D]      _computeReward(i)      (rllib_envs/MARLCattleAviary.py:110)
+ *   terminated  uint8   [E][D+1]    _computeTerminated(i), column D = "__all__"   (:246)
+ *   truncated   uint8   [E][D+1]    _computeTruncated(i),  column D = "__all__"   (:326)
+ *   auto_reset resets an env when either "__all__" flag is set (what RLlib ends an episode on).
  */
 #ifndef CHS_H_
 #define CHS_H_
@@ -32,7 +39,7 @@
 extern "C" {
 #endif
 
-#define CHS_ABI_VERSION 1
+#define CHS_ABI_VERSION 2
 #define CHS_MAX_DRONES 12   /* GLOBAL_MAX_NUM_DRONES, BaseAviary.py:112 */
 #define CHS_NUM_STATS 16
 
@@ -96,6 +103,7 @@ typedef struct ChsDims {
   int32_t action_buffer_size; /* ABS = int(0.15*ctrl_freq), BaseRLAviary.py:69 */
   int32_t reward_width;       /* 1 (CTDE) or max_drones (MARL) */
   int32_t envs_per_block, threads_per_block, smem_bytes;
+  int32_t flag_width;         /* 1 (CTDE) or max_drones + 1 (MARL: one flag per drone, then "__all__") */
 } ChsDims;
 
 /* Host-side, float64, env-major view of the complete simulator state: the fields

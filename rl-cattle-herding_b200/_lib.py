@@ -8,7 +8,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("CHS_LIB", os.path.join(_HERE, "libchs.so"))   # CHS_LIB: build-variant experiments
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 MAX_DRONES = 12
 NUM_STATS = 16
 
@@ -34,7 +34,7 @@ class ChsParams(C.Structure):
 class ChsDims(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("num_envs", "max_drones", "num_cattle", "action_width", "obs_rows",
                                          "obs_len", "substeps", "action_buffer_size", "reward_width",
-                                         "envs_per_block", "threads_per_block", "smem_bytes")]
+                                         "envs_per_block", "threads_per_block", "smem_bytes", "flag_width")]
 
 
 _F64 = ("pos", "quat", "rpy", "vel", "ang_v", "rpy_rates", "last_rpm", "pid_ipos", "pid_last_rpy", "pid_irpy",

@@ -29,11 +29,16 @@ class CattleHerdingBatchedEnv:
     `start_level` (the reference hard-codes 7), `fixed_num_drones` (0 = draw per episode in the level's
     [min,max] like BaseAviary.py:307), `obs_rows` (12 = reference padding), `auto_reset`, `precision`
     ("fp32" product / "fp64" parity instrument), `env_id_offset` (global id of env 0, for sharding), `seed`.
+
+    `packing="marl"` selects the rllib_envs semantics (MARLCattleAviary / BaseMARLAviary): per-drone
+    observation rows without the 12-slot neighbour gap, `reward` (E, D), `terminated` / `truncated` (E, D+1)
+    whose last column is RLlib's "__all__" entry; `auto_reset` fires on either "__all__" flag.
     """
 
     def __init__(self, num_envs, num_drones=3, num_cattle=20, pyb_freq=240, ctrl_freq=30, act="vel",
-                 start_level=7, fixed_num_drones=0, obs_rows=12, auto_reset=True, precision="fp32",
-                 spawn_table=None, device=None, env_id_offset=0, seed=0, envs_per_block=0, threads_per_block=0):
+                 start_level=7, fixed_num_drones=0, obs_rows=None, auto_reset=True, precision="fp32",
+                 spawn_table=None, device=None, env_id_offset=0, seed=0, envs_per_block=0, threads_per_block=0,
+                 packing="ctde"):
         if not torch.cuda.is_available():
             raise RuntimeError("CattleHerdingBatchedEnv needs a CUDA device (there is no CPU fallback)")
         self.lib = _lib.load()
@@ -44,7 +49,10 @@ class CattleHerdingBatchedEnv:
         p.struct_size = C.sizeof(_lib.ChsParams)
         p.num_cattle, p.max_drones, p.fixed_num_drones = int(num_cattle), int(num_drones), int(fixed_num_drones)
         p.pyb_freq, p.ctrl_freq, p.act_type, p.start_level = int(pyb_freq), int(ctrl_freq), act_code, int(start_level)
-        p.obs_rows, p.packing, p.precision = int(obs_rows), 0, {"fp32": 0, "fp64": 1}[precision]
+        self.packing = packing
+        if obs_rows is None:
+            obs_rows = 12 if packing == "ctde" else int(num_drones)
+        p.obs_rows, p.packing, p.precision = int(obs_rows), {"ctde": 0, "marl": 1}[packing], {"fp32": 0, "fp64": 1}[precision]
         p.auto_reset, p.env_id_offset, p.seed = int(bool(auto_reset)), int(env_id_offset), int(seed)
         p.envs_per_block, p.threads_per_block = int(envs_per_block), int(threads_per_block)
         self._h = C.c_void_p(0)
@@ -54,6 +62,7 @@ class CattleHerdingBatchedEnv:
         self.num_envs, self.max_drones, self.num_cattle = d.num_envs, d.max_drones, d.num_cattle
         self.action_width, self.obs_rows, self.obs_len, self.substeps = d.action_width, d.obs_rows, d.obs_len, d.substeps
         assert self.action_width == ACT_WIDTH[act_code]
+        self.reward_width, self.flag_width = d.reward_width, d.flag_width
         self.auto_reset = bool(auto_reset)
         self.precision = precision
         self.ctrl_freq, self.pyb_freq = int(ctrl_freq), int(pyb_freq)
@@ -61,9 +70,12 @@ class CattleHerdingBatchedEnv:
         # tensors owned by the host layer; the kernel writes straight into them
         self.obs = torch.zeros((E, self.obs_rows, self.obs_len), dtype=torch.float32, device=dev)
         self.terminal_obs = torch.zeros_like(self.obs)
-        self.reward = torch.zeros((E,), dtype=torch.float32, device=dev)
-        self.terminated = torch.zeros((E,), dtype=torch.uint8, device=dev)
-        self.truncated = torch.zeros((E,), dtype=torch.uint8, device=dev)
+        rshape = (E,) if packing == "ctde" else (E, self.reward_width)
+        fshape = (E,) if packing == "ctde" else (E, self.flag_width)
+        self._rshape, self._fshape = rshape, fshape
+        self.reward = torch.zeros(rshape, dtype=torch.float32, device=dev)
+        self.terminated = torch.zeros(fshape, dtype=torch.uint8, device=dev)
+        self.truncated = torch.zeros(fshape, dtype=torch.uint8, device=dev)
         self._dbg_nb = self._dbg_herd = None
         self._host = None
         if spawn_table is not None:
@@ -135,9 +147,9 @@ class CattleHerdingBatchedEnv:
             self._host = {
                 "actions": torch.zeros((E, self.max_drones, self.action_width), dtype=torch.float32, **pin),
                 "obs": torch.zeros((E, R, L), dtype=torch.float32, **pin),
-                "reward": torch.zeros((E,), dtype=torch.float32, **pin),
-                "terminated": torch.zeros((E,), dtype=torch.uint8, **pin),
-                "truncated": torch.zeros((E,), dtype=torch.uint8, **pin),
+                "reward": torch.zeros(self._rshape, dtype=torch.float32, **pin),
+                "terminated": torch.zeros(self._fshape, dtype=torch.uint8, **pin),
+                "truncated": torch.zeros(self._fshape, dtype=torch.uint8, **pin),
                 "done_idx": torch.zeros((E,), dtype=torch.int32, **pin),
                 "terminal_obs": torch.zeros((E, R, L), dtype=torch.float32, **pin),
             }

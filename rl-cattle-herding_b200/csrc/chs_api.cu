@@ -89,11 +89,14 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
   if (smem > kSmemCap) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
   DeviceGuard dg(h->device);
   if (h->f64) {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
     CUDA_TRY(cudaFuncSetAttribute(reset_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
   } else {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
     CUDA_TRY(cudaFuncSetAttribute(reset_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
   }
   h->kp.G = G;
@@ -101,6 +104,11 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
   h->smem = smem;
   return CHS_OK;
 }
+
+// per-env widths of the reward and flag outputs: the MARL dicts have one entry per drone, the flag dicts one more
+// for "__all__" (rllib_envs/BaseAviary.py:426-430)
+static inline int reward_width(const ChsHandle* h) { return h->kp.packing == CHS_PACK_MARL ? h->kp.D : 1; }
+static inline int flag_width(const ChsHandle* h) { return h->kp.packing == CHS_PACK_MARL ? h->kp.D + 1 : 1; }
 
 extern "C" int chs_set_launch(ChsHandle* h, int32_t envs_per_block, int32_t threads_per_block) {
   if (!h) return fail(CHS_ERR_INVALID, "null handle");
@@ -119,12 +127,12 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   const int A = action_width(prm->act_type);
   if (A < 0) return fail(CHS_ERR_INVALID, "unknown act_type %d", prm->act_type);
   if (prm->start_level < 0 || prm->start_level >= k::NUM_LEVELS) return fail(CHS_ERR_INVALID, "start_level must be 0..7");
-  if (prm->packing != CHS_PACK_CTDE) return fail(CHS_ERR_INVALID, "only CTDE packing is implemented in this build");
+  if (prm->packing != CHS_PACK_CTDE && prm->packing != CHS_PACK_MARL) return fail(CHS_ERR_INVALID, "unknown packing %d", prm->packing);
   if (prm->aero_flags != 0) return fail(CHS_ERR_INVALID, "aero extras (drag/ground effect/downwash) are not part of Physics.DYN and not implemented yet");
   if (prm->cattle_integrate != 0) return fail(CHS_ERR_INVALID, "cattle_integrate is not implemented yet");
   if (prm->fixed_num_drones < 0 || prm->fixed_num_drones > prm->max_drones)
     return fail(CHS_ERR_INVALID, "fixed_num_drones must be 0..max_drones");
-  int R = prm->obs_rows == 0 ? CHS_MAX_DRONES : prm->obs_rows;
+  int R = prm->obs_rows == 0 ? (prm->packing == CHS_PACK_MARL ? prm->max_drones : CHS_MAX_DRONES) : prm->obs_rows;
   if (R != CHS_MAX_DRONES && R != prm->max_drones) return fail(CHS_ERR_INVALID, "obs_rows must be 12 or max_drones");
   int ndev = 0;
   CUDA_TRY(cudaGetDeviceCount(&ndev));
@@ -223,7 +231,7 @@ extern "C" int chs_get_dims(const ChsHandle* h, ChsDims* out) {
   out->num_envs = h->E; out->max_drones = h->kp.D; out->num_cattle = h->kp.M;
   out->action_width = h->kp.A; out->obs_rows = h->kp.R; out->obs_len = h->kp.L;
   out->substeps = h->kp.K; out->action_buffer_size = (int)(0.15 * h->kp.ctrl_freq);
-  out->reward_width = 1;
+  out->reward_width = reward_width(h); out->flag_width = flag_width(h);
   out->envs_per_block = h->kp.G; out->threads_per_block = h->threads; out->smem_bytes = h->smem;
   return CHS_OK;
 }
@@ -310,13 +318,20 @@ extern "C" int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_d
 
 template <typename T> static void launch_step_variant(ChsHandle* h, const KArgs<T>& a, int grid, cudaStream_t st);
 template <> void launch_step_variant<double>(ChsHandle* h, const KArgs<double>& a, int grid, cudaStream_t st) {
-  step_kernel<double, 512, 1><<<grid, h->threads, h->smem, st>>>(a);
+  if (h->kp.packing == CHS_PACK_MARL) step_kernel<double, 512, 1, true><<<grid, h->threads, h->smem, st>>>(a);
+  else step_kernel<double, 512, 1, false><<<grid, h->threads, h->smem, st>>>(a);
 }
 template <> void launch_step_variant<float>(ChsHandle* h, const KArgs<float>& a, int grid, cudaStream_t st) {
   // latency variant while the grid is under ~512 threads per SM, occupancy variant beyond
   const bool big = (h->reg_variant == 2 && h->threads <= 256) || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
-  if (big) step_kernel<float, 256, 4><<<grid, h->threads, h->smem, st>>>(a);
-  else step_kernel<float, 512, 1><<<grid, h->threads, h->smem, st>>>(a);
+  const bool marl = h->kp.packing == CHS_PACK_MARL;
+  if (big) {
+    if (marl) step_kernel<float, 256, 4, true><<<grid, h->threads, h->smem, st>>>(a);
+    else step_kernel<float, 256, 4, false><<<grid, h->threads, h->smem, st>>>(a);
+  } else {
+    if (marl) step_kernel<float, 512, 1, true><<<grid, h->threads, h->smem, st>>>(a);
+    else step_kernel<float, 512, 1, false><<<grid, h->threads, h->smem, st>>>(a);
+  }
 }
 
 template <typename T>

@@ -186,7 +186,8 @@ __global__ void __launch_bounds__(512) reset_kernel(const KArgs<T> a) {
 // Two register budgets are compiled: MINB = 1 (up to 128 registers per thread, shortest dependent chains, for
 // grids of about one wave where latency decides) and MINB = 4 (64 registers, 4 CTAs of 256 threads per SM, for
 // large batches where issue-slot occupancy decides).  The host picks by grid size.
-template <typename T, int MAXT, int MINB>
+// MARL selects the rllib_envs packing (per-drone reward / flags, sequential reward loop) at compile time.
+template <typename T, int MAXT, int MINB, bool MARL>
 __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const KParams& p = a.p;
@@ -371,48 +372,112 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       }
       const double inv_n = c_inv_n[n];
       const T inv_nT = T(inv_n);
-      csum *= T(0.5) * inv_nT; ssum *= T(0.5) * inv_nT; c2d *= inv_nT;
       const double2 cc = s.ccent[t];
       const double ddx = dcx * inv_n - cc.x, ddy = dcy * inv_n - cc.y;
       const double cent = sqrt(ddx * ddx + ddy * ddy + 0.0);
-      double approach = 0;
-      if (ef.x == ef.x) {   // prev_cent_dists is not None
-        const double change = ef.x - cent;
-        approach = clipv<double>((change / (k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * 5.0, -1.0, 1.0);
-      }
-      ef.x = cent;
       const int herded = s.herd[t];
       const double eff = (M > 0) ? (double)herded / (double)M * 100.0 : 0.0;
-      const double r_global = (double)ssum * c_curr[level][k::C_W_SIMPLE] + (double)csum * c_curr[level][k::C_W_COMPLEX] +
-                              0.1 * c_curr[level][k::C_W_SURV] + approach * c_curr[level][k::C_W_APPROACH] +
-                              (eff / 100.0) * c_curr[level][k::C_W_EFF] + (double)c2d * c_curr[level][k::C_W_C2D];
       const double msd = (double)ms;
-      // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
-      const bool term1 = compute_terminated<double>(level, msd, cent, eff, ef.y);
-      if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
-        ej.y += 1;
-        if (ej.y >= (int)c_curr[level_in][k::C_REQ_TALLY]) {
-          ej.y = 0;
-          level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
+      double r_global = 0;
+      bool term = false, trunc = false;
+      int cause = -1, sc_inc = p.K;
+      if constexpr (!MARL) {
+        double approach = 0;
+        if (ef.x == ef.x) {   // prev_cent_dists is not None
+          const double change = ef.x - cent;
+          approach = clipv<double>((change / (k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * 5.0, -1.0, 1.0);
         }
+        ef.x = cent;
+        csum *= T(0.5) * inv_nT; ssum *= T(0.5) * inv_nT; c2d *= inv_nT;
+        r_global = (double)ssum * c_curr[level][k::C_W_SIMPLE] + (double)csum * c_curr[level][k::C_W_COMPLEX] +
+                   0.1 * c_curr[level][k::C_W_SURV] + approach * c_curr[level][k::C_W_APPROACH] +
+                   (eff / 100.0) * c_curr[level][k::C_W_EFF] + (double)c2d * c_curr[level][k::C_W_C2D];
+        // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
+        const bool term1 = compute_terminated<double>(level, msd, cent, eff, ef.y, 1.0 / 240.0);
+        if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
+          ej.y += 1;
+          if (ej.y >= (int)c_curr[level_in][k::C_REQ_TALLY]) {
+            ej.y = 0;
+            level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
+          }
+        }
+        // second call, the one step() returns (BaseAviary.py:458)
+        term = compute_terminated<double>(level, msd, cent, eff, ef.y, 1.0 / 240.0);
+        // _computeTruncated (:497-552), first hit in the reference's order
+        if (alt_bad) cause = 0;
+        else if (msd < k::COLLISION_THRESHOLD) cause = 1;
+        else if (isolated) cause = 2;
+        else if (cent > k::MISSION_BOUNDARY) cause = 3;
+        else if (ei.x > p.trunc_step_limit) cause = 4;
+        trunc = cause >= 0;
+        a.reward[e] = (float)r_global;
+        a.terminated[e] = term ? 1 : 0;
+        a.truncated[e] = trunc ? 1 : 0;
+      } else {
+        // rllib_envs/BaseAviary.step (:425-430): {i: _computeReward(i)}, then {i: _computeTerminated(i)}, then
+        // {i: _computeTruncated(i)}, each dict built drone by drone.  The reward call is stateful
+        // (MARLCattleAviary.py:110-178): prev_cent_dists is refreshed by the first drone, so later drones see a
+        // zero approach term; every _computeTerminated call advances the spacing clock by 1/CTRL_FREQ; a success
+        // bumps the curriculum tally -- and possibly the level -- before the next drone is rewarded.
+        sc_inc = 1;                                                // `step_counter += 1` (rllib_envs/BaseAviary.py:437)
+        const double clk = 1.0 / (double)p.ctrl_freq;
+        const bool shared_trunc = (cent > k::MISSION_BOUNDARY) || (ei.x > p.trunc_step_limit);
+        float* rw = a.reward + (size_t)e * D;
+        uint8_t* tf = a.terminated + (size_t)e * (D + 1);
+        uint8_t* uf = a.truncated + (size_t)e * (D + 1);
+        bool all_term = true, all_trunc = true;
+        for (int d = 0; d < n; ++d) {
+          const auto A = s.redA[d * G + t];
+          const auto B = s.redB[d * G + t];
+          T s1 = A.x, s2 = A.y, c1 = A.z, c2 = A.w;
+          if (level != level_in) {        // the level moved inside this step: phase 2 used the old targets
+            const T desired = curr<T>(level, k::C_DESIRED), tolf = curr<T>(level, k::C_TOL);
+            s1 = simple_spacing<T>(B.y, desired, tolf); s2 = simple_spacing<T>(B.w, desired, tolf);
+            c1 = complex_spacing<T>(B.y, desired); c2 = complex_spacing<T>(B.w, desired);
+          }
+          double r = (double)((s1 + s2) * T(0.5)) * c_curr[level][k::C_W_SIMPLE] +
+                     (double)((c1 + c2) * T(0.5)) * c_curr[level][k::C_W_COMPLEX] + 0.1 * c_curr[level][k::C_W_SURV];
+          double approach = 0;
+          if (ef.x == ef.x) approach = clipv<double>(((ef.x - cent) / (k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * 5.0, -1.0, 1.0);
+          ef.x = cent;
+          r += approach * c_curr[level][k::C_W_APPROACH];
+          r += (eff / 100.0) * c_curr[level][k::C_W_EFF];
+          r += (double)B.x * c_curr[level][k::C_W_C2D];
+          const bool own_trunc = (B.z != T(0)) || ((double)B.y < k::COLLISION_THRESHOLD) ||
+                                 (B.y > T(k::MAX_FORMATION_DISTANCE)) || shared_trunc;
+          if (compute_terminated<double>(level, msd, cent, eff, ef.y, clk)) {
+            const auto P = s.dpos[d * G + t];
+            const double hx = cc.x - (double)P.x, hy = cc.y - (double)P.y;
+            r += marl_end_of_episode(level, n, (double)B.y, (double)B.w, cent, eff, sqrt(hx * hx + hy * hy));
+            ej.y += 1;
+            if (ej.y >= (int)c_curr[level][k::C_REQ_TALLY]) {
+              ej.y = 0;
+              level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
+            }
+          } else if (own_trunc) {
+            r -= 50.0;
+          }
+          rw[d] = (float)r;
+          r_global += r;
+          uf[d] = own_trunc ? 1 : 0;
+          all_trunc = all_trunc && own_trunc;
+          if (d == 0) cause = (B.z != T(0)) ? 0 : ((double)B.y < k::COLLISION_THRESHOLD) ? 1
+                              : (B.y > T(k::MAX_FORMATION_DISTANCE)) ? 2 : (cent > k::MISSION_BOUNDARY) ? 3 : 4;
+        }
+        for (int d = 0; d < n; ++d) {
+          const bool td = compute_terminated<double>(level, msd, cent, eff, ef.y, clk);
+          tf[d] = td ? 1 : 0;
+          all_term = all_term && td;
+        }
+        for (int d = n; d < D; ++d) { rw[d] = 0.f; tf[d] = 0; uf[d] = 0; }
+        term = all_term; trunc = all_trunc;          // the "__all__" entries (:428,430)
+        tf[D] = term ? 1 : 0; uf[D] = trunc ? 1 : 0;
+        if (!trunc) cause = -1;
       }
       ej.x = level;
-      // second call, the one step() returns (BaseAviary.py:458)
-      const bool term = compute_terminated<double>(level, msd, cent, eff, ef.y);
-      // _computeTruncated (:497-552), first hit in the reference's order
-      int cause = -1;
-      if (alt_bad) cause = 0;
-      else if (msd < k::COLLISION_THRESHOLD) cause = 1;
-      else if (isolated) cause = 2;
-      else if (cent > k::MISSION_BOUNDARY) cause = 3;
-      else if (ei.x > p.trunc_step_limit) cause = 4;
-      const bool trunc = cause >= 0;
-      a.reward[e] = (float)r_global;
-      a.terminated[e] = term ? 1 : 0;
-      a.truncated[e] = trunc ? 1 : 0;
       if (a.dbg_herded) a.dbg_herded[e] = herded;
       double epret = pre_ret + r_global;
-      int sc = ei.x + p.K, scA = ei.y + 1, nn = n, row = ei.w;
+      int sc = ei.x + sc_inc, scA = ei.y + 1, nn = n, row = ei.w;
       fin = term || trunc;
       if (!(r_global == r_global) || fabs(r_global) == Mth<double>::inf()) atomicAdd(a.stats + 9, 1.0);
       if (fin) {

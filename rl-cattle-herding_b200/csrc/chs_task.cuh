@@ -45,7 +45,8 @@ template <typename T> __device__ __forceinline__ T cattle_spacing(T r) {
 
 // Per-drone results handed from the (env, drone) threads to the per-env combine through shared memory.
 //   redA = (simple(d1), simple(d2), complex(d1), complex(d2))
-//   redB = (cattle_spacing(min cow distance), d1 = distance to the nearest other drone, altitude-violation flag, 0)
+//   redB = (cattle_spacing(min cow distance), d1 = distance to the nearest other drone, altitude-violation flag,
+//           d2 = distance to the second nearest)
 // The obs row (BaseRLAviary.py:286-334) is [z rpy vel ang_v | rel-xy of the 2 nearest drones, stable order |
 // zeros up to 12 neighbour slots | rel-xy of cows 0..15 | zeros]; the own-state part is written by the thread
 // that integrated the drone, the neighbour part by drone_neighbors, the cattle part by drone_cattle.  The two
@@ -87,6 +88,7 @@ __device__ __forceinline__ void drone_neighbors(const KParams& p, int g, int d, 
     T* rb = reinterpret_cast<T*>(&s_redB[d * G + g]);
     rb[1] = d1;
     rb[2] = (Mth<T>::abs(me.z - T(k::TARGET_ALT)) > T(k::MAX_ALT_ERROR)) ? T(1) : T(0);
+    rb[3] = d2;
   }
 }
 
@@ -99,7 +101,9 @@ __device__ __forceinline__ void drone_cattle(const KParams& p, int g, int d, boo
   const auto me = s_dpos[d * G + g];
   float* row = s_stage + (size_t)g * p.stage_stride + d * p.L;
   T m2 = Mth<T>::inf();
-  const int cbase = 10 + 2 * CHS_MAX_DRONES;   // neighbours are padded to 12 slots, not 4 (:313-314)
+  // CTDE pads the neighbours to 12 slots, not 4 (sb3_envs/BaseRLAviary.py:313-314); the MARL observation pads
+  // to MAX_NEIGHBORS = 4 (rllib_envs/BaseMARLAviary.py:276-279)
+  const int cbase = (p.packing == CHS_PACK_MARL) ? 10 + 2 * 4 : 10 + 2 * CHS_MAX_DRONES;
   const int nobs = (p.M < 16) ? p.M : 16;
 #pragma unroll 4
   for (int j = 0; j < nobs; ++j) {
@@ -121,15 +125,17 @@ __device__ __forceinline__ void drone_cattle(const KParams& p, int g, int d, boo
   }
 }
 
-// CattleAviary._computeTerminated (:422-492); stateful through the spacing clock (levels 0/1).
-// `ms` = minimum pairwise drone xy spacing, `cent` = centroid distance, `eff` = effectiveness in percent.
+// CattleAviary._computeTerminated (:422-492) and MARLCattleAviary._computeTerminated (:246-321); stateful
+// through the spacing clock (levels 0/1).  `ms` = minimum pairwise drone xy spacing, `cent` = centroid
+// distance, `eff` = effectiveness in percent, `clock_inc` = what one CALL adds to the clock: a hard-coded
+// 1/240 in the CTDE class (:441, two calls per step), 1/CTRL_FREQ in the MARL class (:268, 2N calls per step).
 template <typename T>
-__device__ __forceinline__ bool compute_terminated(int level, T ms, T cent, T eff, T& clock) {
+__device__ __forceinline__ bool compute_terminated(int level, T ms, T cent, T eff, T& clock, T clock_inc) {
   if (level <= 1) {
     const T desired = curr<T>(level, k::C_DESIRED), tol = curr<T>(level, k::C_TOL);
     const T hi = desired + desired * tol, lo = desired - desired * tol;
     if (ms < hi && ms > lo) {
-      clock += T(1.0 / 240.0);           // hard-coded 1/240 per CALL (:441), two calls per step
+      clock += clock_inc;
       if (clock >= curr<T>(level, k::C_HOLD)) return true;
     } else {
       clock = T(0);
@@ -146,6 +152,21 @@ __device__ __forceinline__ bool compute_terminated(int level, T ms, T cent, T ef
     }
   }
   return false;   // level 7 has no branch
+}
+
+// MARLCattleAviary._endOfEpisodeReward (:180-241) for drone `me`; d1/d2 = its two nearest drone distances.
+__device__ __forceinline__ double marl_end_of_episode(int level, int n, double d1, double d2, double cent, double eff,
+                                                      double dist_to_herd) {
+  if (level <= 1 || level == 5) {
+    if (level == 5 && !(eff > c_curr[level][k::C_MIN_EFF])) return 0.0;
+    const double desired = c_curr[level][level == 5 ? k::C_CATTLE_DESIRED : k::C_DESIRED];
+    const double tol = c_curr[level][level == 5 ? k::C_CATTLE_TOL : k::C_TOL];
+    const double hi = desired + desired * tol, lo = desired - desired * tol;
+    return (d1 >= lo && d1 <= hi && d2 >= lo && d2 <= hi) ? 50.0 / (double)n : 0.0;
+  }
+  if (level <= 3) return (cent < c_curr[level][k::C_APPROACH_MIN]) ? 50.0 : 0.0;
+  if (level == 4 || level == 6) return eff * 2 * clipv<double>(1.0 - dist_to_herd / 10.0, 0.0, 1.0);
+  return 0.0;
 }
 
 }  // namespace chs
