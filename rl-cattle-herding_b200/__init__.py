@@ -19,4 +19,7 @@ def __getattr__(name):
     if name in ("BaseAviary", "BaseRLAviary", "CattleAviary"):
         from . import aviary
         return getattr(aviary, name)
+    if name in ("MARLCattleAviary", "RLlibMultiAgentWrapper", "GpuMARLBatchedEnv"):
+        from . import marl_env
+        return getattr(marl_env, name)
     raise AttributeError(name)

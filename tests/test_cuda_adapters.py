@@ -89,3 +89,43 @@ def _pad(a):
         out[: a.shape[0]] = a
         return out
     return a
+
+
+def test_marl_facade_and_rllib_wrapper_against_oracle():
+    """MARLCattleAviary dict contract and the agent_<i> wrapper (rllib_envs/marl_wrapper.py) vs the oracle's step_marl."""
+    import rl_cattle_herding_b200 as pkg
+    M, N = 16, 3
+    table = pkg.spawn.generate(5, M, seed=0)
+    cfg = dict(num_drones=N, num_cattle=M, ctrl_freq=30, fixed_num_drones=N, spawn_table=table, device=0, seed=1, precision="fp64")
+    env = pkg.MARLCattleAviary(**cfg)
+    wrap = pkg.RLlibMultiAgentWrapper(cfg)
+    assert env.observation_space.shape == (66,) and env.action_space.shape == (4,)
+    obs, info = env.reset()
+    wobs, winfo = wrap.reset()
+    assert sorted(obs) == [0, 1, 2] and info == {"__all__": {}} and wrap.agents == ["agent_0", "agent_1", "agent_2"]
+    assert all(np.array_equal(obs[i], wobs[f"agent_{i}"]) for i in range(N))
+    o = co.OracleEnv(M, ctrl_freq=30, start_level=0, spawn_table=table)
+    st = env.sim.get_state()
+    full = {}
+    for k in co.STATE_FIELDS:
+        a = np.asarray(st[k][0])
+        if a.ndim == 2 and a.shape[0] == N and k not in ("cattle_pos", "cattle_vel"):
+            pad = np.zeros((12, a.shape[1])); pad[:N] = a; a = pad
+        full[k] = a
+    o.set_state(full)
+    rng = np.random.default_rng(0)
+    for t in range(12):
+        act = rng.uniform(-1, 1, (N, 4)).astype(np.float32)
+        obs, rew, done, trunc, info = env.step(act)
+        wo, wr, wd, wt, wi = wrap.step({f"agent_{i}": act[i] for i in range(N)})
+        oobs, orew, oterm, otrunc = o.step_marl(act)
+        assert set(done) == {0, 1, 2, "__all__"} and set(trunc) == {0, 1, 2, "__all__"}
+        for i in range(N):
+            assert max_err(obs[i], oobs[i]) <= 4e-6 and abs(rew[i] - orew[i]) <= 2e-7 * (1 + abs(orew[i]))
+            assert done[i] == bool(oterm[i]) and trunc[i] == bool(otrunc[i])
+            assert np.array_equal(wo[f"agent_{i}"], obs[i]) and wr[f"agent_{i}"] == rew[i]
+        assert done["__all__"] == bool(oterm[:N].all()) and trunc["__all__"] == bool(otrunc[:N].all())
+        assert wd["__all__"] == (len(wrap.agents) == 0)
+        if any(trunc.values()) or any(done.values()):
+            break
+    env.close(); wrap.close()
