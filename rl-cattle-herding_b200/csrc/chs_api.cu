@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <cstdlib>
 #include <vector>
 
 #include "../../include/chs.h"
@@ -40,6 +41,7 @@ struct ChsHandle {
   void *drone, *rpm, *cpos, *cvel, *envf, *epret, *spawn;
   int4 *envi, *envj;
   double* stats;
+  double* tab;
   int *dbg_nb, *dbg_herd;
   long long* dbg_clock;
   int threads, smem;
@@ -83,7 +85,9 @@ static const int kSmemCap = 200 * 1024;
 static int configure_launch(ChsHandle* h, int G, int threads) {
   if (G < 1 || G > 32 || (G & (G - 1))) return fail(CHS_ERR_INVALID, "envs_per_block must be a power of two in 1..32");
   if (threads < 32 || threads > 512 || (threads & 31)) return fail(CHS_ERR_INVALID, "threads_per_block must be a multiple of 32 in 32..512");
-  const int smem = smem_for(h, G);
+  int smem = smem_for(h, G);
+  // experiment knob: unused extra shared memory per CTA to lower the number of resident CTAs per SM
+  if (const char* pad = getenv("CHS_SMEM_PAD")) smem += atoi(pad);
   // the opt-in limit is a per-function, process-wide attribute: always raise it to the cap so that handles with
   // different shared-memory needs can coexist (the launch's own size decides occupancy)
   if (smem > kSmemCap) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
@@ -100,6 +104,7 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
     CUDA_TRY(cudaFuncSetAttribute(reset_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
   }
   h->kp.G = G;
+  h->kp.cp_ok = h->f64 ? 1 : ((G >= 2 && (h->E & 1) == 0) ? 1 : 0);
   h->threads = threads;
   h->smem = smem;
   return CHS_OK;
@@ -169,6 +174,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   if ((kp.stage_stride & 31) == 0) kp.stage_stride += 4;
   kp.vec4_ok = ((kp.R * kp.L) % 4 == 0) ? 1 : 0;
   kp.cattle_integrate = 0;
+  kp.act4_ok = (A == 4) ? 1 : 0;
   kp.seed_lo = (uint32_t)(prm->seed & 0xffffffffu); kp.seed_hi = (uint32_t)(prm->seed >> 32);
 
   DeviceGuard dg(device);
@@ -186,6 +192,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   ALLOC0(h->envi, E * sizeof(int4));
   ALLOC0(h->envj, E * sizeof(int4));
   ALLOC0(h->stats, CHS_NUM_STATS * sizeof(double));
+  ALLOC0(h->tab, 152 * sizeof(double));
 #undef ALLOC0
   if (err != cudaSuccess) {
     chs_destroy(h);
@@ -201,6 +208,13 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
       err = cudaMemcpy(h->envf, ef.data(), E * sizeof(double2), cudaMemcpyHostToDevice);
     }
     if (err != cudaSuccess) { chs_destroy(h); return fail(CHS_ERR_CUDA, "state initialisation failed: %s", cudaGetErrorString(err)); }
+  }
+  {
+    std::vector<double> tab(152, 0.0);
+    for (int l = 0; l < k::NUM_LEVELS; ++l) for (int c = 0; c < k::C_NCOLS; ++c) tab[l * k::C_NCOLS + c] = h_curr[l][c];
+    for (int n = 1; n <= CHS_MAX_DRONES; ++n) tab[CHS_TAB_INV_N + n] = 1.0 / n;
+    err = cudaMemcpy(h->tab, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (err != cudaSuccess) { chs_destroy(h); return fail(CHS_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(err)); }
   }
   // launch shape: enough CTAs to cover the 148 SMs a few times over, shared memory permitting
   int G = prm->envs_per_block, threads = prm->threads_per_block;
@@ -218,7 +232,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
 extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
-  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats,
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab,
                   h->d_actions, h->d_obs, h->d_reward, h->d_termobs, h->d_term, h->d_trunc, h->d_mask, h->d_count, h->d_idx};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_count) cudaFreeHost(h->h_count);
@@ -290,7 +304,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.drone = (typename VT<T>::v4*)h->drone; a.rpm = (typename VT<T>::v4*)h->rpm;
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
   a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret;
-  a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats;
+  a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats; a.tab = h->tab;
   a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd; a.dbg_clock = h->dbg_clock;
   return a;
 }
@@ -352,6 +366,7 @@ extern "C" int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, 
   if (!actions_dev || !reward_dev || !terminated_dev || !truncated_dev)
     return fail(CHS_ERR_INVALID, "actions, reward, terminated and truncated pointers are required");
   if (h->kp.auto_reset && !h->spawn_set) return fail(CHS_ERR_STATE, "auto_reset needs a spawn table");
+  if (h->kp.act4_ok && !aligned16(actions_dev)) return fail(CHS_ERR_INVALID, "actions_dev must be 16-byte aligned");
   if (h->kp.vec4_ok && ((obs_dev && !aligned16(obs_dev)) || (terminal_obs_dev && !aligned16(terminal_obs_dev))))
     return fail(CHS_ERR_INVALID, "obs buffers must be 16-byte aligned");
   DeviceGuard dg(h->device);

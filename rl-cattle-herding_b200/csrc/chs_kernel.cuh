@@ -30,6 +30,7 @@ template <typename T> struct Smem {
   typename VT<T>::v2* u;
   float* stage;
   double2* ccent;   // herd centroid per env
+  double* ctab;     // curriculum rows + 1/n (chs_task.cuh)
   int* n; int* herd; int* done; int* newn; int* row; int* flist; int* termrow; int* dlist; int* epi; int* level;
   int* misc;   // [0] number of flock-active envs, [1] number of finished envs
 };
@@ -45,6 +46,7 @@ template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* ba
   s.u = reinterpret_cast<typename VT<T>::v2*>(base + l.off_u);
   s.stage = reinterpret_cast<float*>(base + l.off_stage);
   s.ccent = reinterpret_cast<double2*>(base + l.off_ccent);
+  s.ctab = reinterpret_cast<double*>(base + l.off_ctab);
   int* ib = reinterpret_cast<int*>(base + l.off_int);
   s.n = ib + 32 * I_N; s.herd = ib + 32 * I_HERD; s.done = ib + 32 * I_DONE; s.newn = ib + 32 * I_NEWN;
   s.row = ib + 32 * I_ROW; s.flist = ib + 32 * I_FLOCK; s.termrow = ib + 32 * I_TERMROW; s.dlist = ib + 32 * I_DLIST; s.epi = ib + 32 * I_EPI; s.level = ib + 32 * I_LEVEL;
@@ -54,17 +56,33 @@ template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* ba
 
 __device__ __forceinline__ int ilog2_pow2(int g) { return 31 - __clz(g); }
 
+// 16-byte asynchronous global->shared copy (LDGSTS); bytes past `src_bytes` (0..16) are zero-filled.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 // Copies the staged rows of env g (plus zero padding up to R*L floats) to dst, one warp per env.
 __device__ __forceinline__ void copy_rows(const KParams& p, const float* stage_g, float* dst, int lane) {
   const int RL = p.R * p.L;
   if (p.vec4_ok) {
     const float4* src4 = reinterpret_cast<const float4*>(stage_g);
     float4* dst4 = reinterpret_cast<float4*>(dst);
-    const int nq = RL >> 2, sq = p.stage_stride >> 2;
-    for (int r = lane; r < nq; r += 32) {
-      const float4 v = (r < sq) ? src4[r] : make_float4(0.f, 0.f, 0.f, 0.f);
-      __stcs(dst4 + r, v);
+    const int nq = RL >> 2;
+    const int sq = min(p.stage_stride >> 2, nq);
+    // staged part: two independent LDS -> STG pairs in flight per lane; zero padding: stores only
+    int r = lane;
+    for (; r + 32 < sq; r += 64) {
+      const float4 v0 = src4[r], v1 = src4[r + 32];
+      __stcs(dst4 + r, v0);
+      __stcs(dst4 + r + 32, v1);
     }
+    if (r < sq) { __stcs(dst4 + r, src4[r]); r += 32; }
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (; r < nq; r += 32) __stcs(dst4 + r, z);
   } else {
     const int DL = p.D * p.L;
     for (int r = lane; r < RL; r += 32) __stcs(dst + r, r < DL ? stage_g[r] : 0.f);
@@ -137,7 +155,7 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
     const int g = s.dlist[it % nd], d = it / nd;
     const int n = s.n[g];
     if (d < n) {
-      drone_neighbors<T>(p, g, d, n, 0, false, s.dpos, s.redA, s.redB, s.stage, nullptr);
+      drone_neighbors<T>(p, nullptr, g, d, n, 0, false, s.dpos, s.redA, s.redB, s.stage, nullptr);
       drone_cattle<T>(p, g, d, false, s.dpos, s.cpos, s.redB, s.stage);
     }
   }
@@ -201,7 +219,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   int ndt = (DG + 31) & ~31;          // "drone" threads: the first warps of the CTA
   if (ndt > nt) ndt = nt;
 
-#define CHS_STAMP(i) do { if (a.dbg_clock && t == 0) a.dbg_clock[(size_t)blockIdx.x * 8 + (i)] = clock64(); } while (0)
+#define CHS_STAMP(i) do { if (a.dbg_clock && t == 0) a.dbg_clock[(size_t)blockIdx.x * 16 + (i)] = clock64(); } while (0)
   CHS_STAMP(0);
   // ---------------- phase 0 ----------------
   // Every global read the step needs is issued here, before the first barrier, so that the DRAM round trips
@@ -209,6 +227,12 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   int4 pre_i = make_int4(0, 0, 0, 0), pre_j = make_int4(0, 0, 0, 0);
   double2 pre_f = make_double2(0.0, 0.0);
   double pre_ret = 0.0;
+  const bool env_lane = (t < G) && (e0 + t < E);      // warp 0 only (G <= 32)
+  if (env_lane) {
+    // env scalars are fetched once, here, and stay in registers until phase 3
+    const int e = e0 + t;
+    pre_i = a.envi[e]; pre_j = a.envj[e]; pre_f = a.envf[e]; pre_ret = a.epret[e];
+  }
   DroneState<T> ds0;
   float act0[4] = {0.f, 0.f, 0.f, 0.f};
   const bool have0 = (t < ndt) && (t < DG) && (e0 + (t & (G - 1)) < E);
@@ -216,37 +240,62 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     const int g = t & (G - 1), d = t >> lg, e = e0 + g;
     load_drone<T>(a, d, e, ds0);
     const float* ap = a.actions + ((size_t)e * D + d) * p.A;
+    if (p.A == 4 && p.act4_ok) {
+      const float4 v = *reinterpret_cast<const float4*>(ap);
+      act0[0] = v.x; act0[1] = v.y; act0[2] = v.z; act0[3] = v.w;
+    } else {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) if (i < p.A) act0[i] = ap[i];
+      for (int i = 0; i < 4; ++i) if (i < p.A) act0[i] = ap[i];
+    }
   }
   {
+    using V2 = typename VT<T>::v2;
+    if (p.cp_ok) {
+      // herd rows -> shared memory as 16-byte asynchronous copies (no register staging, all in flight at once);
+      // envs past the end of the batch are zero-filled through the src-size operand
+      constexpr int EPC = 16 / (int)sizeof(V2);            // envs per 16-byte chunk
+      const int cpr = G / EPC;                             // chunks per cow row
+      const int nchunk = 2 * M * cpr;
+      for (int it = t; it < nchunk; it += nt) {
+        const int arr = (it >= M * cpr) ? 1 : 0;
+        const int r = it - arr * M * cpr;
+        const int j = r / cpr, c = r - j * cpr;
+        const int eb = e0 + c * EPC;
+        int valid = E - eb; valid = valid < 0 ? 0 : (valid > EPC ? EPC : valid);
+        const V2* src = (arr ? a.cvel : a.cpos) + (size_t)j * E + (valid > 0 ? eb : e0);
+        V2* dst = (arr ? s.cvel : s.cpos) + j * G + c * EPC;
+        cp_async16(dst, src, valid * (int)sizeof(V2));
+      }
+    }
+    // curriculum table: 76 chunks of 16 bytes
+    for (int it = t; it < 76; it += nt) cp_async16(s.ctab + 2 * it, a.tab + 2 * it, 16);
+    cp_async_commit();
     const int nq = (G * p.stage_stride) >> 2;
     float4* st4 = reinterpret_cast<float4*>(s.stage);
     for (int i = t; i < nq; i += nt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int it = t; it < M * G; it += nt) {
-      const int g = it & (G - 1), j = it >> lg, e = e0 + g;
-      if (e < E) { s.cpos[it] = a.cpos[(size_t)j * E + e]; s.cvel[it] = a.cvel[(size_t)j * E + e]; }
-      else { s.cpos[it] = mk2<T>(0, 0); s.cvel[it] = mk2<T>(0, 0); }
+    if (!p.cp_ok) {
+      for (int it = t; it < M * G; it += nt) {
+        const int g = it & (G - 1), j = it >> lg, e = e0 + g;
+        if (e < E) { s.cpos[it] = a.cpos[(size_t)j * E + e]; s.cvel[it] = a.cvel[(size_t)j * E + e]; }
+        else { s.cpos[it] = mk2<T>(0, 0); s.cvel[it] = mk2<T>(0, 0); }
+      }
     }
     if (t < 32) {
       bool fl = false;
-      const int e = e0 + t;
       if (t < G) {
         int n = 0;
-        if (e < E) {
-          // env scalars are fetched once, here, and stay in registers until phase 3
-          pre_i = a.envi[e]; pre_j = a.envj[e]; pre_f = a.envf[e]; pre_ret = a.epret[e];
-          n = pre_i.z; fl = (((pre_i.y + 1) & 1) == 0);
-        }
+        if (env_lane) { n = pre_i.z; fl = (((pre_i.y + 1) & 1) == 0); }
         s.n[t] = n; s.herd[t] = 0; s.done[t] = 0; s.level[t] = pre_j.x;
       }
       const unsigned m = __ballot_sync(0xffffffffu, fl);
       if (fl) s.flist[__popc(m & ((1u << t) - 1u))] = t;
       if (t == 0) { s.misc[0] = __popc(m); s.misc[1] = 0; }
     }
+    cp_async_wait_all();
   }
-  __syncthreads();
   CHS_STAMP(1);
+  __syncthreads();
+  CHS_STAMP(2);
 
   // ---------------- phase 1 ----------------
   const int nact = s.misc[0];
@@ -302,8 +351,9 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       }
     }
   }
+  CHS_STAMP(3);
   __syncthreads();
-  CHS_STAMP(2);
+  CHS_STAMP(4);
 
   // ---------------- phase 2 ----------------
   // per-drone pieces: neighbour ranking + spacing rewards on the drone threads, cattle pieces on threads half a
@@ -313,7 +363,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       const int n = s.n[g];
       if (e < E && d < n)
-        drone_neighbors<T>(p, g, d, n, s.level[g], true, s.dpos, s.redA, s.redB, s.stage,
+        drone_neighbors<T>(p, s.ctab, g, d, n, s.level[g], true, s.dpos, s.redA, s.redB, s.stage,
                            a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr);
     }
   }
@@ -339,8 +389,9 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       if (cow_inside<T>(s.dpos, n, g, G, c.x, c.y)) atomicAdd(&s.herd[g], 1);
     }
   }
+  CHS_STAMP(5);
   __syncthreads();
-  CHS_STAMP(3);
+  CHS_STAMP(6);
 
   // ---------------- phase 3 ----------------
   if (t < 32) {
@@ -370,11 +421,12 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         alt_bad = alt_bad || (B.z != T(0));
         dcx += (double)P.x; dcy += (double)P.y;
       }
-      const double inv_n = c_inv_n[n];
+      const double inv_n = s.ctab[CHS_TAB_INV_N + n];
       const T inv_nT = T(inv_n);
       const double2 cc = s.ccent[t];
       const double ddx = dcx * inv_n - cc.x, ddy = dcy * inv_n - cc.y;
       const double cent = sqrt(ddx * ddx + ddy * ddy + 0.0);
+      CHS_STAMP(7);
       const int herded = s.herd[t];
       const double eff = (M > 0) ? (double)herded / (double)M * 100.0 : 0.0;
       const double msd = (double)ms;
@@ -389,20 +441,20 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         }
         ef.x = cent;
         csum *= T(0.5) * inv_nT; ssum *= T(0.5) * inv_nT; c2d *= inv_nT;
-        r_global = (double)ssum * c_curr[level][k::C_W_SIMPLE] + (double)csum * c_curr[level][k::C_W_COMPLEX] +
-                   0.1 * c_curr[level][k::C_W_SURV] + approach * c_curr[level][k::C_W_APPROACH] +
-                   (eff / 100.0) * c_curr[level][k::C_W_EFF] + (double)c2d * c_curr[level][k::C_W_C2D];
+        r_global = (double)ssum * s.ctab[level * k::C_NCOLS + k::C_W_SIMPLE] + (double)csum * s.ctab[level * k::C_NCOLS + k::C_W_COMPLEX] +
+                   0.1 * s.ctab[level * k::C_NCOLS + k::C_W_SURV] + approach * s.ctab[level * k::C_NCOLS + k::C_W_APPROACH] +
+                   (eff / 100.0) * s.ctab[level * k::C_NCOLS + k::C_W_EFF] + (double)c2d * s.ctab[level * k::C_NCOLS + k::C_W_C2D];
         // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
-        const bool term1 = compute_terminated<double>(level, msd, cent, eff, ef.y, 1.0 / 240.0);
+        const bool term1 = compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, 1.0 / 240.0);
         if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
           ej.y += 1;
-          if (ej.y >= (int)c_curr[level_in][k::C_REQ_TALLY]) {
+          if (ej.y >= (int)s.ctab[level_in * k::C_NCOLS + k::C_REQ_TALLY]) {
             ej.y = 0;
             level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
           }
         }
         // second call, the one step() returns (BaseAviary.py:458)
-        term = compute_terminated<double>(level, msd, cent, eff, ef.y, 1.0 / 240.0);
+        term = compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, 1.0 / 240.0);
         // _computeTruncated (:497-552), first hit in the reference's order
         if (alt_bad) cause = 0;
         else if (msd < k::COLLISION_THRESHOLD) cause = 1;
@@ -431,26 +483,26 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
           const auto B = s.redB[d * G + t];
           T s1 = A.x, s2 = A.y, c1 = A.z, c2 = A.w;
           if (level != level_in) {        // the level moved inside this step: phase 2 used the old targets
-            const T desired = curr<T>(level, k::C_DESIRED), tolf = curr<T>(level, k::C_TOL);
+            const T desired = curr<T>(s.ctab, level, k::C_DESIRED), tolf = curr<T>(s.ctab, level, k::C_TOL);
             s1 = simple_spacing<T>(B.y, desired, tolf); s2 = simple_spacing<T>(B.w, desired, tolf);
             c1 = complex_spacing<T>(B.y, desired); c2 = complex_spacing<T>(B.w, desired);
           }
-          double r = (double)((s1 + s2) * T(0.5)) * c_curr[level][k::C_W_SIMPLE] +
-                     (double)((c1 + c2) * T(0.5)) * c_curr[level][k::C_W_COMPLEX] + 0.1 * c_curr[level][k::C_W_SURV];
+          double r = (double)((s1 + s2) * T(0.5)) * s.ctab[level * k::C_NCOLS + k::C_W_SIMPLE] +
+                     (double)((c1 + c2) * T(0.5)) * s.ctab[level * k::C_NCOLS + k::C_W_COMPLEX] + 0.1 * s.ctab[level * k::C_NCOLS + k::C_W_SURV];
           double approach = 0;
           if (ef.x == ef.x) approach = clipv<double>(((ef.x - cent) / (k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * 5.0, -1.0, 1.0);
           ef.x = cent;
-          r += approach * c_curr[level][k::C_W_APPROACH];
-          r += (eff / 100.0) * c_curr[level][k::C_W_EFF];
-          r += (double)B.x * c_curr[level][k::C_W_C2D];
+          r += approach * s.ctab[level * k::C_NCOLS + k::C_W_APPROACH];
+          r += (eff / 100.0) * s.ctab[level * k::C_NCOLS + k::C_W_EFF];
+          r += (double)B.x * s.ctab[level * k::C_NCOLS + k::C_W_C2D];
           const bool own_trunc = (B.z != T(0)) || ((double)B.y < k::COLLISION_THRESHOLD) ||
                                  (B.y > T(k::MAX_FORMATION_DISTANCE)) || shared_trunc;
-          if (compute_terminated<double>(level, msd, cent, eff, ef.y, clk)) {
+          if (compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, clk)) {
             const auto P = s.dpos[d * G + t];
             const double hx = cc.x - (double)P.x, hy = cc.y - (double)P.y;
-            r += marl_end_of_episode(level, n, (double)B.y, (double)B.w, cent, eff, sqrt(hx * hx + hy * hy));
+            r += marl_end_of_episode(s.ctab, level, n, (double)B.y, (double)B.w, cent, eff, sqrt(hx * hx + hy * hy));
             ej.y += 1;
-            if (ej.y >= (int)c_curr[level][k::C_REQ_TALLY]) {
+            if (ej.y >= (int)s.ctab[level * k::C_NCOLS + k::C_REQ_TALLY]) {
               ej.y = 0;
               level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
             }
@@ -465,7 +517,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
                               : (B.y > T(k::MAX_FORMATION_DISTANCE)) ? 2 : (cent > k::MISSION_BOUNDARY) ? 3 : 4;
         }
         for (int d = 0; d < n; ++d) {
-          const bool td = compute_terminated<double>(level, msd, cent, eff, ef.y, clk);
+          const bool td = compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, clk);
           tf[d] = td ? 1 : 0;
           all_term = all_term && td;
         }
@@ -475,6 +527,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         if (!trunc) cause = -1;
       }
       ej.x = level;
+      CHS_STAMP(8);
       if (a.dbg_herded) a.dbg_herded[e] = herded;
       double epret = pre_ret + r_global;
       int sc = ei.x + sc_inc, scA = ei.y + 1, nn = n, row = ei.w;
@@ -509,8 +562,9 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     if (fin) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
     if (t == 0) { s.misc[1] = __popc(m); if (blockIdx.x == 0) atomicAdd(a.stats + 10, (double)E); }
   }
+  CHS_STAMP(9);
   __syncthreads();
-  CHS_STAMP(4);
+  CHS_STAMP(10);
 
   // ---------------- phase 4 ----------------
   const int nd = s.misc[1];
@@ -528,12 +582,12 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       if (dst) copy_rows(p, s.stage + (size_t)g * p.stage_stride, dst, lane);
     }
   }
-  CHS_STAMP(5);
+  CHS_STAMP(11);
   // ---------------- phase 5 ----------------
   if (nd > 0) {
     reset_envs<T>(a, s, e0, nd);
   }
-  CHS_STAMP(6);
+  CHS_STAMP(12);
 #undef CHS_STAMP
 }
 

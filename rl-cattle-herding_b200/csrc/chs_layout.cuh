@@ -35,6 +35,8 @@ struct KParams {
   int stage_stride;      // floats per env in the obs staging area (>= D*L, multiple of 4)
   int vec4_ok;           // (R*L) % 4 == 0 -> float4 copy-out
   int cattle_integrate;
+  int cp_ok;             // herd rows can be staged with 16-byte cp.async (alignment of row segments)
+  int act4_ok;           // A == 4: one float4 load per action row
   uint32_t seed_lo, seed_hi;
 };
 
@@ -50,6 +52,7 @@ template <typename T> struct KArgs {
   double* epret;
   const typename VT<T>::v2* spawn;   // [n_sims][spawn_stride]
   double* stats;                     // [CHS_NUM_STATS]
+  const double* tab;                 // [CHS_TAB_DOUBLES] curriculum rows + 1/n (chs_task.cuh)
   // per-call
   const float* actions;              // [E][D][A]
   float* obs;                        // [E][R][L]
@@ -63,12 +66,12 @@ template <typename T> struct KArgs {
   const uint8_t* reset_mask;         // reset kernel only (nullable = all)
   int* dbg_neighbors;                // nullable [E][D][2]
   int* dbg_herded;                   // nullable [E]
-  long long* dbg_clock;              // nullable [grid][8]: clock64() of thread 0 at each phase boundary
+  long long* dbg_clock;              // nullable [grid][16]: clock64() of thread 0 at phase and sub-phase boundaries
 };
 
 // ---- shared-memory carve-up (per CTA of G envs) ----------------------------------------------------
 struct SmemLayout {
-  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_ccent, off_int, total;
+  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_ccent, off_ctab, off_int, total;
 };
 
 template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, int M, int G, int stage_stride) {
@@ -84,6 +87,7 @@ template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, i
   o = (o + 15) & ~15;
   s.off_stage = o; o += G * stage_stride * 4;
   s.off_ccent = o; o += G * 16;
+  s.off_ctab = o; o += 152 * 8;         // CHS_TAB_DOUBLES (149) rounded up
   s.off_int = o;  o += (10 * 32 + 8) * 4;  // ten per-env int arrays [32] + misc
   s.total = o;
   return s;

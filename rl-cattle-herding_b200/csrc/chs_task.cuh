@@ -5,13 +5,14 @@
 
 namespace chs {
 
-__constant__ double c_curr[k::NUM_LEVELS][k::C_NCOLS] = {CHS_CURRICULUM_ROWS};
+// The curriculum rows and 1/n (n = 0..12 drones) live in one float64 table in global memory (KArgs::tab,
+// CHS_TAB_DOUBLES entries, filled by the host from CHS_CURRICULUM_ROWS) that every CTA copies to shared memory in
+// phase 0, together with its other loads.  A __constant__ table indexed by the per-env level costs a constant-
+// cache miss (a DRAM round trip when L2 is cold) on the serial per-env path; the shared copy costs one LDS.
+constexpr int CHS_TAB_INV_N = k::NUM_LEVELS * k::C_NCOLS;
+constexpr int CHS_TAB_DOUBLES = CHS_TAB_INV_N + CHS_MAX_DRONES + 1;
 
-// 1/n for n = 0..12 drones (n = 0 never divides)
-__constant__ double c_inv_n[CHS_MAX_DRONES + 1] = {0.0, 1.0, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7,
-                                                   1.0 / 8, 1.0 / 9, 1.0 / 10, 1.0 / 11, 1.0 / 12};
-
-template <typename T> __device__ __forceinline__ T curr(int level, int col) { return T(c_curr[level][col]); }
+template <typename T> __device__ __forceinline__ T curr(const double* ct, int level, int col) { return T(ct[level * k::C_NCOLS + col]); }
 
 // CattleAviary.SimpleSpacingReward (:594-626)
 template <typename T> __device__ __forceinline__ T simple_spacing(T r, T desired, T tolfrac) {
@@ -53,7 +54,7 @@ template <typename T> __device__ __forceinline__ T cattle_spacing(T r) {
 // functions touch disjoint shared-memory words, so different threads may run them concurrently.
 
 template <typename T>
-__device__ __forceinline__ void drone_neighbors(const KParams& p, int g, int d, int n, int level, bool want_reward,
+__device__ __forceinline__ void drone_neighbors(const KParams& p, const double* ct, int g, int d, int n, int level, bool want_reward,
                                                 const typename VT<T>::v4* s_dpos, typename VT<T>::v4* s_redA,
                                                 typename VT<T>::v4* s_redB, float* s_stage, int* dbg_nb /* nullable: [2] */) {
   const int G = p.G;
@@ -82,7 +83,7 @@ __device__ __forceinline__ void drone_neighbors(const KParams& p, int g, int d, 
   }
   if (dbg_nb) { dbg_nb[0] = j1; dbg_nb[1] = j2; }
   if (want_reward) {
-    const T desired = curr<T>(level, k::C_DESIRED), tolf = curr<T>(level, k::C_TOL);
+    const T desired = curr<T>(ct, level, k::C_DESIRED), tolf = curr<T>(ct, level, k::C_TOL);
     s_redA[d * G + g] = mk4<T>(simple_spacing<T>(d1, desired, tolf), simple_spacing<T>(d2, desired, tolf),
                                complex_spacing<T>(d1, desired), complex_spacing<T>(d2, desired));
     T* rb = reinterpret_cast<T*>(&s_redB[d * G + g]);
@@ -130,23 +131,23 @@ __device__ __forceinline__ void drone_cattle(const KParams& p, int g, int d, boo
 // distance, `eff` = effectiveness in percent, `clock_inc` = what one CALL adds to the clock: a hard-coded
 // 1/240 in the CTDE class (:441, two calls per step), 1/CTRL_FREQ in the MARL class (:268, 2N calls per step).
 template <typename T>
-__device__ __forceinline__ bool compute_terminated(int level, T ms, T cent, T eff, T& clock, T clock_inc) {
+__device__ __forceinline__ bool compute_terminated(const double* ct, int level, T ms, T cent, T eff, T& clock, T clock_inc) {
   if (level <= 1) {
-    const T desired = curr<T>(level, k::C_DESIRED), tol = curr<T>(level, k::C_TOL);
+    const T desired = curr<T>(ct, level, k::C_DESIRED), tol = curr<T>(ct, level, k::C_TOL);
     const T hi = desired + desired * tol, lo = desired - desired * tol;
     if (ms < hi && ms > lo) {
       clock += clock_inc;
-      if (clock >= curr<T>(level, k::C_HOLD)) return true;
+      if (clock >= curr<T>(ct, level, k::C_HOLD)) return true;
     } else {
       clock = T(0);
     }
   } else if (level <= 3) {
-    if (cent < curr<T>(level, k::C_APPROACH_MIN)) return true;
+    if (cent < curr<T>(ct, level, k::C_APPROACH_MIN)) return true;
   } else if (level == 4 || level == 6) {
-    if (eff > curr<T>(level, k::C_MIN_EFF)) return true;
+    if (eff > curr<T>(ct, level, k::C_MIN_EFF)) return true;
   } else if (level == 5) {
-    if (eff > curr<T>(level, k::C_MIN_EFF)) {
-      const T desired = curr<T>(level, k::C_CATTLE_DESIRED), tol = curr<T>(level, k::C_CATTLE_TOL);
+    if (eff > curr<T>(ct, level, k::C_MIN_EFF)) {
+      const T desired = curr<T>(ct, level, k::C_CATTLE_DESIRED), tol = curr<T>(ct, level, k::C_CATTLE_TOL);
       const T hi = desired + desired * tol, lo = desired - desired * tol;
       if (ms < hi && ms > lo) return true;
     }
@@ -155,16 +156,16 @@ __device__ __forceinline__ bool compute_terminated(int level, T ms, T cent, T ef
 }
 
 // MARLCattleAviary._endOfEpisodeReward (:180-241) for drone `me`; d1/d2 = its two nearest drone distances.
-__device__ __forceinline__ double marl_end_of_episode(int level, int n, double d1, double d2, double cent, double eff,
+__device__ __forceinline__ double marl_end_of_episode(const double* ct, int level, int n, double d1, double d2, double cent, double eff,
                                                       double dist_to_herd) {
   if (level <= 1 || level == 5) {
-    if (level == 5 && !(eff > c_curr[level][k::C_MIN_EFF])) return 0.0;
-    const double desired = c_curr[level][level == 5 ? k::C_CATTLE_DESIRED : k::C_DESIRED];
-    const double tol = c_curr[level][level == 5 ? k::C_CATTLE_TOL : k::C_TOL];
+    if (level == 5 && !(eff > ct[level * k::C_NCOLS + (k::C_MIN_EFF)])) return 0.0;
+    const double desired = ct[level * k::C_NCOLS + (level == 5 ? k::C_CATTLE_DESIRED : k::C_DESIRED)];
+    const double tol = ct[level * k::C_NCOLS + (level == 5 ? k::C_CATTLE_TOL : k::C_TOL)];
     const double hi = desired + desired * tol, lo = desired - desired * tol;
     return (d1 >= lo && d1 <= hi && d2 >= lo && d2 <= hi) ? 50.0 / (double)n : 0.0;
   }
-  if (level <= 3) return (cent < c_curr[level][k::C_APPROACH_MIN]) ? 50.0 : 0.0;
+  if (level <= 3) return (cent < ct[level * k::C_NCOLS + (k::C_APPROACH_MIN)]) ? 50.0 : 0.0;
   if (level == 4 || level == 6) return eff * 2 * clipv<double>(1.0 - dist_to_herd / 10.0, 0.0, 1.0);
   return 0.0;
 }

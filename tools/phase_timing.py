@@ -19,13 +19,13 @@ env = pkg.CattleHerdingBatchedEnv(E, num_drones=N, num_cattle=M, fixed_num_drone
                                   device=0, envs_per_block=G, threads_per_block=TH)
 env.reset()
 grid = (E + G - 1) // G
-clk = torch.zeros((grid, 8), dtype=torch.int64, device="cuda")
+clk = torch.zeros((grid, 16), dtype=torch.int64, device="cuda")
 acts = [torch.rand((E, N, 4), device="cuda") * 2 - 1 for _ in range(8)]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for i in range(40):
     env.step(acts[i % 8])
 pkg._lib.check(env.lib.chs_set_phase_clock(env._h, C.c_void_p(clk.data_ptr())))
-acc = np.zeros(6)
+acc = np.zeros(12)
 tot = 0.0
 R = 20
 for i in range(R):
@@ -33,11 +33,12 @@ for i in range(R):
     env.step(acts[i % 8])
     torch.cuda.synchronize()
     c = clk.cpu().numpy().astype(np.float64)
-    d = np.diff(c[:, :7], axis=1)
+    d = np.diff(c[:, :13], axis=1)
     acc += d.mean(axis=0)
-    tot += (c[:, 6].max() - c[:, 0].min())
-names = ["p0 load", "p1 drone|alpha", "p2 reduce|finish", "p3 per-env", "p4 copy-out", "p5 reset"]
+    tot += 0
+names = ["p0 issue+fill", "p0 barrier", "p1 thread0 chain", "p1 barrier", "p2 thread0 work", "p2 barrier", "p3 reduce+cent",
+         "p3 reward/flags", "p3 stores+stats", "p3 barrier", "p4 copy-out", "p5 reset"]
 print(f"E={E} G={G} threads={TH} grid={grid}: mean cycles per phase (avg over CTAs, {R} steps)")
 for n, v in zip(names, acc / R):
     print(f"  {n:18s} {v:9.0f} cyc")
-print(f"  sum {acc.sum() / R:.0f} cyc; kernel span (max end - min start over CTAs) {tot / R:.0f} cyc")
+print(f"  sum {acc.sum() / R:.0f} cyc")
