@@ -82,8 +82,8 @@ typedef struct ChsParams {
   int32_t precision;          /* 0 = fp32 (product), 1 = fp64 (parity instrument) */
   int32_t auto_reset;         /* 1: finished envs are reset inside chs_step (VecEnv semantics) */
   int32_t aero_flags;         /* bit0 drag, bit1 ground effect, bit2 downwash (BaseAviary.py:943-1039;
-                                 not part of Physics.DYN, off by default) */
-  int32_t cattle_integrate;   /* non-reference extension: pos += vel*CTRL_TIMESTEP after flocking */
+                                 PYB-only in the reference, here forces of the DYN step; 0 = reference DYN) */
+  int32_t cattle_integrate;   /* non-reference extension: herd pos += vel*CTRL_TIMESTEP every control step */
   int32_t env_id_offset;      /* global id of local env 0 (multi-GPU sharding by env index) */
   int32_t envs_per_block;     /* launch tuning, 0 = auto */
   int32_t threads_per_block;  /* launch tuning, 0 = auto */

@@ -54,6 +54,7 @@ GRAVITY = G * M_KG                        # BaseAviary.py:162
 HOVER_RPM = math.sqrt(GRAVITY / (4 * KF))  # BaseAviary.py:163
 MAX_RPM = math.sqrt((T2W * GRAVITY) / (4 * KF))  # BaseAviary.py:164
 MAX_THRUST = 4 * KF * MAX_RPM ** 2        # BaseAviary.py:165
+PROP_XY = ((0.028, -0.028), (-0.028, -0.028), (-0.028, 0.028), (0.028, 0.028))   # cf2x.urdf:42,54,66,78
 GND_EFF_H_CLIP = 0.25 * PROP_RADIUS * math.sqrt((15 * MAX_RPM ** 2 * KF * GND_EFF_COEFF) / MAX_THRUST)  # :173
 TARGET_ALT = 0.45                         # BaseAviary.py:111
 SPEED_LIMIT = 0.3 * MAX_SPEED_KMH * (1000 / 3600)  # BaseRLAviary.py:102
@@ -163,7 +164,7 @@ class OracleEnv:
     """One environment, CTDE (sb3_envs) packing.  All arithmetic in float64 like the reference."""
 
     def __init__(self, n_cattle, ctrl_freq=30, pyb_freq=240, start_level=7, spawn_table=None,
-                 act="vel"):
+                 act="vel", aero_flags=0, cattle_integrate=False):
         if pyb_freq % ctrl_freq != 0:
             raise ValueError("pyb_freq is not divisible by ctrl_freq")  # BaseAviary.py:102-103
         self.M = int(n_cattle)
@@ -176,6 +177,9 @@ class OracleEnv:
         self.ACTION_SPACE = {"vel": 4, "rpm": 4, "pid": 3, "one_d_rpm": 1, "one_d_pid": 1}[act]  # BaseRLAviary.py:115-123
         self.L = 10 + MAX_NEIGHBORS * 2 + MAX_NEARBY_CATTLE * 2 + self.ABS * self.ACTION_SPACE  # BaseRLAviary.py:262
         self.act = act
+        # non-reference extensions, both off on the reference's DYN path
+        self.aero_flags = int(aero_flags)            # bit0 drag, bit1 ground effect, bit2 downwash
+        self.cattle_integrate = bool(cattle_integrate)
         row = CURRICULUM[start_level]
         # fixed at construction, never refreshed when the level changes (CattleAviary.py:66,72-73)
         self.EPISODE_LEN_SEC = row[C_EP_LEN]
@@ -360,15 +364,39 @@ class OracleEnv:
     # ---------------------------------------------------------------------------------------------
     # DYN integrator  (BaseAviary.py:1043-1117) + pybullet store semantics (:704-721)
     # ---------------------------------------------------------------------------------------------
-    def _dynamics(self, k, rpm, aero=None):
+    def _dynamics(self, k, rpm, drag_rpm=None, pos0=None):
+        """BaseAviary._dynamics (:1043-1102).  With `aero_flags` the PYB-only models of :943-1039 are added
+        as forces of the same explicit step (they have no DYN counterpart in the reference, so this restatement
+        defines them):
+          ground effect (:943-978)  per-prop extra thrust kf rpm_i^2 c_g (r_p / 4 h_i)^2, h_i = world height of
+                                    prop i clipped at GND_EFF_H_CLIP; applied at the props, so it also enters the
+                                    x/y torques; gate |roll|,|pitch| < pi/2 <=> R[2][2] > 0
+          drag (:982-1009)          world force -(c_xy, c_xy, c_z) * v * sum(2 pi rpm'/60); rpm' is
+                                    last_clipped_action (:437,447): the previous control step's RPMs on the first
+                                    substep, the current ones afterwards (R^T then LINK_FRAME cancel)
+          downwash (:1013-1039)     body-z force -a exp(-(dxy/b)^2/2) from every drone above within 10 m; the
+                                    other drones' positions are sampled once per control step (`pos0`)."""
         dt = self.PYB_DT
         pos = self.pos[k]; quat = tuple(self.quat[k]); vel = self.vel[k]; w = self.rpy_rates[k]
         R = quat_to_matrix(quat)
         f = [r * r * KF for r in rpm]
+        if (self.aero_flags & 2) and R[2][2] > 0:
+            for i, (ox, oy) in enumerate(PROP_XY):
+                h = max(pos[2] + R[2][0] * ox + R[2][1] * oy, GND_EFF_H_CLIP)
+                f[i] = f[i] + rpm[i] * rpm[i] * KF * GND_EFF_COEFF * (PROP_RADIUS / (4 * h)) ** 2
         thrust = f[0] + f[1] + f[2] + f[3]
+        if (self.aero_flags & 4) and pos0 is not None:
+            for i in range(self.n_drones):
+                dz = pos0[i][2] - pos[2]
+                dxy = math.sqrt((pos0[i][0] - pos[0]) ** 2 + (pos0[i][1] - pos[1]) ** 2)
+                if i != k and dz > 0 and dxy < 10:
+                    wgt = math.exp(-0.5 * (dxy / (DW2 * dz + DW3)) ** 2)
+                    if wgt > 0:
+                        thrust = thrust - DW1 * (PROP_RADIUS / (4 * dz)) ** 2 * wgt
         fw = [R[0][2] * thrust, R[1][2] * thrust, R[2][2] * thrust - GRAVITY]
-        if aero is not None:                      # optional extras, SURVEY 8(f) rank 1 (off for DYN)
-            fw = [fw[i] + aero[i] for i in range(3)]
+        if (self.aero_flags & 1) and drag_rpm is not None:
+            om = (2 * math.pi / 60) * (drag_rpm[0] + drag_rpm[1] + drag_rpm[2] + drag_rpm[3])
+            fw = [fw[0] - DRAG_XY * om * vel[0], fw[1] - DRAG_XY * om * vel[1], fw[2] - DRAG_Z * om * vel[2]]
         zt = [r * r * KM for r in rpm]
         tz = -zt[0] + zt[1] - zt[2] + zt[3]
         tx = (f[0] + f[1] - f[2] - f[3]) * (ARM / math.sqrt(2))
@@ -858,14 +886,17 @@ class OracleEnv:
         self.step_counter_A += 1
         n = self.n_drones
         rpm = self.preprocess_action(np.asarray(action))
-        for _ in range(self.K):
+        pos0 = self.pos.copy() if (self.aero_flags & 4) else None
+        for sub in range(self.K):
             for k in range(n):
-                self._dynamics(k, rpm[k])
+                self._dynamics(k, rpm[k], self.last_rpm[k] if sub == 0 else rpm[k], pos0)
             self.last_rpm[:n] = rpm
         for k in range(n):
             self.rpy[k] = quat_to_euler(tuple(self.quat[k]))
         if self.step_counter_A % 2 == 0:
             self.flocking_step()
+        if self.cattle_integrate:       # non-reference kinematic herd
+            self.cattle_pos[:, :2] = self.cattle_pos[:, :2] + self.cattle_vel[:, :2] * self.CTRL_DT
         obs = np.zeros((NMAX, self.L), dtype=np.float32)
         rew = np.zeros(NMAX)
         term = np.zeros(NMAX, dtype=bool)
@@ -888,14 +919,17 @@ class OracleEnv:
         self.step_counter_A += 1
         n = self.n_drones
         rpm = self.preprocess_action(np.asarray(action))
-        for _ in range(self.K):
+        pos0 = self.pos.copy() if (self.aero_flags & 4) else None
+        for sub in range(self.K):
             for k in range(n):
-                self._dynamics(k, rpm[k])
+                self._dynamics(k, rpm[k], self.last_rpm[k] if sub == 0 else rpm[k], pos0)
             self.last_rpm[:n] = rpm
         for k in range(n):
             self.rpy[k] = quat_to_euler(tuple(self.quat[k]))
         if self.step_counter_A % 2 == 0:
             self.flocking_step()
+        if self.cattle_integrate:       # non-reference kinematic herd
+            self.cattle_pos[:, :2] = self.cattle_pos[:, :2] + self.cattle_vel[:, :2] * self.CTRL_DT
         obs = self.compute_obs()
         reward = self.compute_reward()
         terminated = self.compute_terminated()

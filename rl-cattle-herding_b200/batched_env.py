@@ -30,6 +30,10 @@ class CattleHerdingBatchedEnv:
     [min,max] like BaseAviary.py:307), `obs_rows` (12 = reference padding), `auto_reset`, `precision`
     ("fp32" product / "fp64" parity instrument), `env_id_offset` (global id of env 0, for sharding), `seed`.
 
+    Non-reference options, both off by default: `aero` (bit mask or names "drag", "ground_effect", "downwash":
+    the PYB-only aerodynamic models of sb3_envs/BaseAviary.py:943-1039 as forces of the DYN step) and
+    `cattle_integrate` (herd positions advance by vel * CTRL_TIMESTEP every control step).
+
     `packing="marl"` selects the rllib_envs semantics (MARLCattleAviary / BaseMARLAviary): per-drone
     observation rows without the 12-slot neighbour gap, `reward` (E, D), `terminated` / `truncated` (E, D+1)
     whose last column is RLlib's "__all__" entry; `auto_reset` fires on either "__all__" flag.
@@ -38,7 +42,7 @@ class CattleHerdingBatchedEnv:
     def __init__(self, num_envs, num_drones=3, num_cattle=20, pyb_freq=240, ctrl_freq=30, act="vel",
                  start_level=7, fixed_num_drones=0, obs_rows=None, auto_reset=True, precision="fp32",
                  spawn_table=None, device=None, env_id_offset=0, seed=0, envs_per_block=0, threads_per_block=0,
-                 packing="ctde"):
+                 packing="ctde", aero=0, cattle_integrate=False):
         if not torch.cuda.is_available():
             raise RuntimeError("CattleHerdingBatchedEnv needs a CUDA device (there is no CPU fallback)")
         self.lib = _lib.load()
@@ -50,6 +54,10 @@ class CattleHerdingBatchedEnv:
         p.num_cattle, p.max_drones, p.fixed_num_drones = int(num_cattle), int(num_drones), int(fixed_num_drones)
         p.pyb_freq, p.ctrl_freq, p.act_type, p.start_level = int(pyb_freq), int(ctrl_freq), act_code, int(start_level)
         self.packing = packing
+        if not isinstance(aero, int):       # names -> ChsParams.aero_flags bits
+            aero = sum({"drag": 1, "ground_effect": 2, "downwash": 4}[str(x)] for x in aero)
+        p.aero_flags, p.cattle_integrate = int(aero), int(bool(cattle_integrate))
+        self.aero_flags, self.cattle_integrate = int(aero), bool(cattle_integrate)
         if obs_rows is None:
             obs_rows = 12 if packing == "ctde" else int(num_drones)
         p.obs_rows, p.packing, p.precision = int(obs_rows), {"ctde": 0, "marl": 1}[packing], {"fp32": 0, "fp64": 1}[precision]

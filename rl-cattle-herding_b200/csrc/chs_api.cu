@@ -133,8 +133,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   if (A < 0) return fail(CHS_ERR_INVALID, "unknown act_type %d", prm->act_type);
   if (prm->start_level < 0 || prm->start_level >= k::NUM_LEVELS) return fail(CHS_ERR_INVALID, "start_level must be 0..7");
   if (prm->packing != CHS_PACK_CTDE && prm->packing != CHS_PACK_MARL) return fail(CHS_ERR_INVALID, "unknown packing %d", prm->packing);
-  if (prm->aero_flags != 0) return fail(CHS_ERR_INVALID, "aero extras (drag/ground effect/downwash) are not part of Physics.DYN and not implemented yet");
-  if (prm->cattle_integrate != 0) return fail(CHS_ERR_INVALID, "cattle_integrate is not implemented yet");
+  if (prm->aero_flags < 0 || prm->aero_flags > 7) return fail(CHS_ERR_INVALID, "aero_flags must be a combination of bits 0..2");
   if (prm->fixed_num_drones < 0 || prm->fixed_num_drones > prm->max_drones)
     return fail(CHS_ERR_INVALID, "fixed_num_drones must be 0..max_drones");
   int R = prm->obs_rows == 0 ? (prm->packing == CHS_PACK_MARL ? prm->max_drones : CHS_MAX_DRONES) : prm->obs_rows;
@@ -173,7 +172,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   kp.stage_stride = (kp.D * kp.L + 3) & ~3;
   if ((kp.stage_stride & 31) == 0) kp.stage_stride += 4;
   kp.vec4_ok = ((kp.R * kp.L) % 4 == 0) ? 1 : 0;
-  kp.cattle_integrate = 0;
+  kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
+  kp.aero_flags = prm->aero_flags;
   kp.act4_ok = (A == 4) ? 1 : 0;
   kp.seed_lo = (uint32_t)(prm->seed & 0xffffffffu); kp.seed_hi = (uint32_t)(prm->seed >> 32);
 

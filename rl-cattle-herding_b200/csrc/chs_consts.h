@@ -27,6 +27,8 @@ constexpr double GND_EFF_COEFF = 11.36859;
 constexpr double PROP_RADIUS = 2.31348e-2;
 constexpr double DRAG_XY = 9.1785e-7, DRAG_Z = 10.311e-7;
 constexpr double DW1 = 2267.18, DW2 = 0.16, DW3 = -0.11;
+// 0.25 r_p sqrt(15 MAX_RPM^2 kf c_g / MAX_THRUST) = 0.25 r_p sqrt(15 c_g / 4)   (BaseAviary.py:173)
+constexpr double GND_EFF_H_CLIP = 0.03776371349209501;
 
 // ---- control/DSLPIDControl.py:37-53 -------------------------------------------------------------
 constexpr double P_FOR[3] = {0.4, 0.4, 1.25};

@@ -196,4 +196,95 @@ __device__ __forceinline__ void dyn_substeps(DroneState<T>& s, const T rpm[4], i
   quat_to_euler<T>(s.q, s.rpy);
 }
 
+// The same K substeps with the opt-in aerodynamic extras (ChsParams.aero_flags).  The
+// reference has these models for its PYB_* modes only (sb3_envs/BaseAviary.py:943-1039); as forces of the explicit
+// DYN step they are defined by oracle/cattle_oracle.py:_dynamics, which this function follows term by term:
+//   bit1 ground effect (:943-978)  per-prop extra thrust kf rpm_i^2 c_g (r_p/(4 h_i))^2, h_i = world height of
+//        prop i (cf2x.urdf:42-78) clipped at GND_EFF_H_CLIP, gate |roll|,|pitch| < pi/2 <=> R[2][2] > 0; applied
+//        at the props, so it enters the x/y torques too
+//   bit0 drag (:982-1009)          world force -(c_xy,c_xy,c_z) * v * sum(2 pi rpm'/60), rpm' = RPMs of the
+//        previous control step on the first substep, the current ones afterwards (:437,447)
+//   bit2 downwash (:1013-1039)     body-z force -a exp(-(dxy/b)^2/2) from every drone above within 10 m; the other
+//        drones' positions are the snapshot `others[j*G]` taken at the start of the control step
+// Kept out of line: the DYN path proper does not pay registers or instruction-cache space for it.
+template <typename T>
+__device__ __noinline__ void dyn_substeps_aero(DroneState<T>& s, const T* rpm, const T* prev_rpm, int K, T dt, int flags,
+                                               const typename VT<T>::v4* others, int G, int n, int self) {
+  T f0[4], zt[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const T r2 = rpm[i] * rpm[i]; f0[i] = r2 * T(k::KF); zt[i] = r2 * T(k::KM); }
+  const T tz = -zt[0] + zt[1] - zt[2] + zt[3];
+  const T PX[4] = {T(0.028), T(-0.028), T(-0.028), T(0.028)};
+  const T PY[4] = {T(-0.028), T(-0.028), T(0.028), T(0.028)};
+  T R[3][3];
+  for (int it = 0; it < K; ++it) {
+    quat_to_matrix<T>(s.q, R);
+    T f[4] = {f0[0], f0[1], f0[2], f0[3]};
+    if ((flags & 2) && R[2][2] > T(0)) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const T h = Mth<T>::max(s.p[2] + R[2][0] * PX[i] + R[2][1] * PY[i], T(k::GND_EFF_H_CLIP));
+        const T q = T(k::PROP_RADIUS) / (T(4) * h);
+        f[i] = f[i] + rpm[i] * rpm[i] * T(k::KF) * T(k::GND_EFF_COEFF) * (q * q);
+      }
+    }
+    T thrust = f[0] + f[1] + f[2] + f[3];
+    if (flags & 4) {
+      for (int j = 0; j < n; ++j) {
+        const auto o = others[j * G];
+        const T dz = o.z - s.p[2];
+        const T ex = o.x - s.p[0], ey = o.y - s.p[1];
+        const T dxy = Mth<T>::sqrt_exact(ex * ex + ey * ey);
+        if (j != self && dz > T(0) && dxy < T(10)) {
+          const T u = dxy / (T(k::DW2) * dz + T(k::DW3));
+          const T wgt = Mth<T>::exp(T(-0.5) * (u * u));
+          if (wgt > T(0)) {
+            const T q = T(k::PROP_RADIUS) / (T(4) * dz);
+            thrust = thrust - T(k::DW1) * (q * q) * wgt;
+          }
+        }
+      }
+    }
+    T fw[3] = {R[0][2] * thrust, R[1][2] * thrust, R[2][2] * thrust - T(k::GRAVITY)};
+    if (flags & 1) {
+      const T* dr = (it == 0) ? prev_rpm : rpm;
+      const T om = T(2.0 * k::PI / 60.0) * (dr[0] + dr[1] + dr[2] + dr[3]);
+      fw[0] = fw[0] - T(k::DRAG_XY) * om * s.v[0];
+      fw[1] = fw[1] - T(k::DRAG_XY) * om * s.v[1];
+      fw[2] = fw[2] - T(k::DRAG_Z) * om * s.v[2];
+    }
+    const T tx = (f[0] + f[1] - f[2] - f[3]) * T(k::ARM / k::SQRT2);
+    const T ty = (-f[0] + f[1] + f[2] - f[3]) * T(k::ARM / k::SQRT2);
+    const T Jw[3] = {T(k::IXX) * s.w[0], T(k::IYY) * s.w[1], T(k::IZZ) * s.w[2]};
+    const T cr[3] = {s.w[1] * Jw[2] - s.w[2] * Jw[1], s.w[2] * Jw[0] - s.w[0] * Jw[2], s.w[0] * Jw[1] - s.w[1] * Jw[0]};
+    const T wd[3] = {(tx - cr[0]) * T(1.0 / k::IXX), (ty - cr[1]) * T(1.0 / k::IYY), (tz - cr[2]) * T(1.0 / k::IZZ)};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s.v[i] = s.v[i] + dt * (fw[i] * T(1.0 / k::M_KG));
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s.w[i] = s.w[i] + dt * wd[i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s.p[i] = s.p[i] + dt * s.v[i];
+    const T wn = Mth<T>::sqrt(s.w[0] * s.w[0] + s.w[1] * s.w[1] + s.w[2] * s.w[2]);
+    T x = s.q[0], y = s.q[1], z = s.q[2], ww = s.q[3];
+    if (!(wn <= T(1e-8))) {
+      const T pp = s.w[0], qq = s.w[1], rr = s.w[2];
+      T sn, c;
+      Mth<T>::sincos_small(wn * dt * T(0.5), &sn, &c);
+      const T sc = sn * Mth<T>::frcp(wn);
+      const T nx = c * x + sc * (rr * y - qq * z + pp * ww);
+      const T ny = c * y + sc * (-rr * x + pp * z + qq * ww);
+      const T nz = c * z + sc * (qq * x - pp * y + rr * ww);
+      const T nw = c * ww + sc * (-pp * x - qq * y - rr * z);
+      x = nx; y = ny; z = nz; ww = nw;
+    }
+    const T in = Mth<T>::rsqrt(x * x + y * y + z * z + ww * ww);
+    s.q[0] = x * in; s.q[1] = y * in; s.q[2] = z * in; s.q[3] = ww * in;
+  }
+  if (K > 0) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s.av[i] = R[i][0] * s.w[0] + R[i][1] * s.w[1] + R[i][2] * s.w[2];
+  }
+  quat_to_euler<T>(s.q, s.rpy);
+}
+
 }  // namespace chs

@@ -267,6 +267,13 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         cp_async16(dst, src, valid * (int)sizeof(V2));
       }
     }
+    if (p.aero_flags & 4) {   // downwash: start-of-step positions of every drone, parked in redA until phase 2
+      const size_t st = (size_t)D * E;
+      for (int it = t; it < DG; it += nt) {
+        const int g = it & (G - 1), d = it >> lg, e = e0 + g;
+        if (e < E) s.redA[it] = a.drone[F_A * st + (size_t)d * E + e];
+      }
+    }
     // curriculum table: 76 chunks of 16 bytes
     for (int it = t; it < 76; it += nt) cp_async16(s.ctab + 2 * it, a.tab + 2 * it, 16);
     cp_async_commit();
@@ -317,7 +324,13 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         }
         T rpm[4];
         action_to_rpm<T>(p, ds, act, ctrl_dt, rpm);
-        dyn_substeps<T>(ds, rpm, p.K, pyb_dt);
+        if (p.aero_flags) {
+          const auto pr = a.rpm[(size_t)d * E + e];
+          const T prev[4] = {pr.x, pr.y, pr.z, pr.w};
+          dyn_substeps_aero<T>(ds, rpm, prev, p.K, pyb_dt, p.aero_flags, s.redA + g, G, s.n[g], d);
+        } else {
+          dyn_substeps<T>(ds, rpm, p.K, pyb_dt);
+        }
         store_drone<T>(a, d, e, ds);
         a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
         s.dpos[it] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], T(0));
@@ -358,6 +371,35 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   // ---------------- phase 2 ----------------
   // per-drone pieces: neighbour ranking + spacing rewards on the drone threads, cattle pieces on threads half a
   // CTA away so that the two halves run on different warps
+  if (p.cattle_integrate) {
+    // non-reference kinematic herd: velocities first, then pos += vel * CTRL_TIMESTEP for
+    // every cow of every env, then the herd centroid again; obs / reward / effectiveness below see the new positions
+    for (int it = t; it < nact * M; it += nt) {
+      const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
+      const auto ua = s.u[i * G + g];
+      const auto v = herd_finish<T>(s.dpos, s.n[g], g, G, s.cpos[i * G + g], s.cvel[i * G + g], ua.x, ua.y);
+      a.cvel[(size_t)i * E + e] = v;
+      s.cvel[i * G + g] = v;
+    }
+    __syncthreads();
+    for (int it = t; it < M * G; it += nt) {
+      const int g = it & (G - 1), j = it >> lg, e = e0 + g;
+      if (e < E) {
+        const auto c = s.cpos[it];
+        const auto v = s.cvel[it];
+        const auto nc = mk2<T>(c.x + v.x * ctrl_dt, c.y + v.y * ctrl_dt);
+        s.cpos[it] = nc;
+        a.cpos[(size_t)j * E + e] = nc;
+      }
+    }
+    __syncthreads();
+    if (t < G) {
+      double cx = 0, cy = 0;
+      for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + t]; cx += (double)c.x; cy += (double)c.y; }
+      const double inv_m = 1.0 / (double)M;
+      s.ccent[t] = make_double2(cx * inv_m, cy * inv_m);
+    }
+  }
   if (t < ndt) {
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
@@ -375,11 +417,13 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       if (e < E && d < s.n[g]) drone_cattle<T>(p, g, d, true, s.dpos, s.cpos, s.redB, s.stage);
     }
   }
-  for (int it = t; it < nact * M; it += nt) {
-    const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
-    const auto ua = s.u[i * G + g];
-    const auto v = herd_finish<T>(s.dpos, s.n[g], g, G, s.cpos[i * G + g], s.cvel[i * G + g], ua.x, ua.y);
-    a.cvel[(size_t)i * E + e] = v;       // positions are not advanced on the DYN path
+  if (!p.cattle_integrate) {
+    for (int it = t; it < nact * M; it += nt) {
+      const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
+      const auto ua = s.u[i * G + g];
+      const auto v = herd_finish<T>(s.dpos, s.n[g], g, G, s.cpos[i * G + g], s.cvel[i * G + g], ua.x, ua.y);
+      a.cvel[(size_t)i * E + e] = v;       // positions are not advanced on the DYN path
+    }
   }
   for (int it = t; it < M * G; it += nt) {
     const int g = it & (G - 1);

@@ -34,7 +34,8 @@ struct KParams {
   int env_id_offset;
   int stage_stride;      // floats per env in the obs staging area (>= D*L, multiple of 4)
   int vec4_ok;           // (R*L) % 4 == 0 -> float4 copy-out
-  int cattle_integrate;
+  int cattle_integrate;  // non-reference: herd positions advance by vel * CTRL_TIMESTEP every control step
+  int aero_flags;        // bit0 drag, bit1 ground effect, bit2 downwash (chs_drone.cuh: dyn_substeps_aero)
   int cp_ok;             // herd rows can be staged with 16-byte cp.async (alignment of row segments)
   int act4_ok;           // A == 4: one float4 load per action row
   uint32_t seed_lo, seed_hi;

@@ -50,6 +50,7 @@ template <> struct Mth<float> {
   static __device__ __forceinline__ float abs(float x) { return fabsf(x); }
   static __device__ __forceinline__ float min(float a, float b) { return fminf(a, b); }
   static __device__ __forceinline__ float max(float a, float b) { return fmaxf(a, b); }
+  static __device__ __forceinline__ float sqrt_exact(float x) { return sqrtf(x); }
   static __device__ __forceinline__ float inf() { return __int_as_float(0x7f800000); }
   static __device__ __forceinline__ float nan() { return __int_as_float(0x7fc00000); }
 };
@@ -70,6 +71,7 @@ template <> struct Mth<double> {
   static __device__ __forceinline__ double abs(double x) { return ::fabs(x); }
   static __device__ __forceinline__ double min(double a, double b) { return ::fmin(a, b); }
   static __device__ __forceinline__ double max(double a, double b) { return ::fmax(a, b); }
+  static __device__ __forceinline__ double sqrt_exact(double x) { return ::sqrt(x); }
   static __device__ __forceinline__ double inf() { return __longlong_as_double(0x7ff0000000000000LL); }
   static __device__ __forceinline__ double nan() { return __longlong_as_double(0x7ff8000000000000LL); }
 };
