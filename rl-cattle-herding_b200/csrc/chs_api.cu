@@ -73,7 +73,7 @@ static int action_width(int act) {
 }
 
 template <typename T> static SmemLayout layout_for(const KParams& kp, int G) {
-  return smem_layout<T>(kp.D, kp.M, G, kp.stage_stride);
+  return smem_layout<T>(kp.D, kp.M, G, kp.stage_stride, kp.zero_bytes);
 }
 
 static int smem_for(const ChsHandle* h, int G) {
@@ -172,6 +172,11 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   kp.stage_stride = (kp.D * kp.L + 3) & ~3;
   if ((kp.stage_stride & 31) == 0) kp.stage_stride += 4;
   kp.vec4_ok = ((kp.R * kp.L) % 4 == 0) ? 1 : 0;
+  kp.bulk_ok = (kp.vec4_ok && !getenv("CHS_NO_BULK")) ? 1 : 0;
+  {
+    const int total = kp.R * kp.L * 4, c1 = kp.stage_stride * 4 < total ? kp.stage_stride * 4 : total;
+    kp.zero_bytes = kp.bulk_ok ? total - c1 : 0;
+  }
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
   kp.aero_flags = prm->aero_flags;
   kp.act4_ok = (A == 4) ? 1 : 0;

@@ -31,12 +31,13 @@ template <typename T> struct Smem {
   float* stage;
   double2* ccent;   // herd centroid per env
   double* ctab;     // curriculum rows + 1/n (chs_task.cuh)
+  float* zeros;     // zero block, source of the obs padding for bulk stores
   int* n; int* herd; int* done; int* newn; int* row; int* flist; int* termrow; int* dlist; int* epi; int* level;
   int* misc;   // [0] number of flock-active envs, [1] number of finished envs
 };
 
 template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* base, const KParams& p) {
-  const SmemLayout l = smem_layout<T>(p.D, p.M, p.G, p.stage_stride);
+  const SmemLayout l = smem_layout<T>(p.D, p.M, p.G, p.stage_stride, p.zero_bytes);
   Smem<T> s;
   s.dpos = reinterpret_cast<typename VT<T>::v4*>(base + l.off_dpos);
   s.redA = reinterpret_cast<typename VT<T>::v4*>(base + l.off_redA);
@@ -47,6 +48,7 @@ template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* ba
   s.stage = reinterpret_cast<float*>(base + l.off_stage);
   s.ccent = reinterpret_cast<double2*>(base + l.off_ccent);
   s.ctab = reinterpret_cast<double*>(base + l.off_ctab);
+  s.zeros = reinterpret_cast<float*>(base + l.off_zero);
   int* ib = reinterpret_cast<int*>(base + l.off_int);
   s.n = ib + 32 * I_N; s.herd = ib + 32 * I_HERD; s.done = ib + 32 * I_DONE; s.newn = ib + 32 * I_NEWN;
   s.row = ib + 32 * I_ROW; s.flist = ib + 32 * I_FLOCK; s.termrow = ib + 32 * I_TERMROW; s.dlist = ib + 32 * I_DLIST; s.epi = ib + 32 * I_EPI; s.level = ib + 32 * I_LEVEL;
@@ -61,6 +63,26 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
 }
+// Bulk (TMA) shared->global store: one thread moves a whole staged observation with two instructions, no LSU
+// traffic.  Sizes and both addresses are multiples of 16 bytes (KParams::bulk_ok).  The generic-proxy writes that
+// filled the staging area are ordered before the async-proxy read by fence.proxy.async after the CTA barrier.
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, unsigned bytes) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(ssrc);
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(sa), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// One env's observation image = staged rows followed by zero padding (from the CTA's zero block) up to R*L floats.
+__device__ __forceinline__ void bulk_copy_rows(const KParams& p, const float* stage_g, const float* zeros, float* dst) {
+  const unsigned total = (unsigned)(p.R * p.L) * 4u;
+  unsigned c1 = (unsigned)p.stage_stride * 4u;
+  if (c1 > total) c1 = total;
+  bulk_store(dst, stage_g, c1);
+  if (total > c1) bulk_store(reinterpret_cast<char*>(dst) + c1, zeros, total - c1);
+}
+
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -107,6 +129,7 @@ template <typename T>
 __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0, int nd) {
   const KParams& p = a.p;
   const int t = threadIdx.x, nt = blockDim.x, G = p.G, E = p.E;
+  for (int i = t; i < (p.zero_bytes >> 4); i += nt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   __syncthreads();   // the copy-out of the terminal observations has finished reading the staging area
   const int sq = p.stage_stride >> 2;
   for (int it = t; it < nd * sq; it += nt) {
@@ -160,7 +183,15 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
     }
   }
   __syncthreads();
-  if (a.obs) {
+  if (a.obs && p.bulk_ok) {
+    if (t < nd) {
+      const int g = s.dlist[t];
+      fence_async_smem();
+      bulk_copy_rows(p, s.stage + (size_t)g * p.stage_stride, s.zeros, a.obs + (size_t)(e0 + g) * p.R * p.L);
+      bulk_commit();
+      bulk_wait_read();
+    }
+  } else if (a.obs) {
     const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
     for (int i = warp; i < nd; i += nwarp) {
       const int g = s.dlist[i];
@@ -280,6 +311,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     const int nq = (G * p.stage_stride) >> 2;
     float4* st4 = reinterpret_cast<float4*>(s.stage);
     for (int i = t; i < nq; i += nt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = t; i < (p.zero_bytes >> 4); i += nt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (!p.cp_ok) {
       for (int it = t; it < M * G; it += nt) {
         const int g = it & (G - 1), j = it >> lg, e = e0 + g;
@@ -327,7 +359,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         if (p.aero_flags) {
           const auto pr = a.rpm[(size_t)d * E + e];
           const T prev[4] = {pr.x, pr.y, pr.z, pr.w};
-          dyn_substeps_aero<T>(ds, rpm, prev, p.K, pyb_dt, p.aero_flags, s.redA + g, G, s.n[g], d);
+          DroneState<T> tmp = ds;      // the out-of-line call takes an address: keep `ds` itself in registers
+          T rp[4] = {rpm[0], rpm[1], rpm[2], rpm[3]};
+          dyn_substeps_aero<T>(tmp, rp, prev, p.K, pyb_dt, p.aero_flags, s.redA + g, G, s.n[g], d);
+          ds = tmp;
         } else {
           dyn_substeps<T>(ds, rpm, p.K, pyb_dt);
         }
@@ -454,6 +489,8 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       T ssum = 0, csum = 0, c2d = 0, ms = Mth<T>::inf();
       double dcx = 0, dcy = 0;
       bool alt_bad = false, isolated = false;
+      CHS_STAMP(13);
+#pragma unroll 1
       for (int d = 0; d < n; ++d) {
         const auto A = s.redA[d * G + t];
         const auto B = s.redB[d * G + t];
@@ -465,6 +502,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         alt_bad = alt_bad || (B.z != T(0));
         dcx += (double)P.x; dcy += (double)P.y;
       }
+      CHS_STAMP(14);
       const double inv_n = s.ctab[CHS_TAB_INV_N + n];
       const T inv_nT = T(inv_n);
       const double2 cc = s.ccent[t];
@@ -601,6 +639,20 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       a.envj[e] = ej;
       a.envf[e] = ef;
       a.epret[e] = epret;
+      if (p.bulk_ok) {
+        // phase 4 folded in: this thread knows where its env's observation goes and ships it with two bulk stores
+        const size_t RL = (size_t)p.R * p.L;
+        float* dst = a.obs ? a.obs + (size_t)e * RL : nullptr;
+        if (fin) {
+          dst = nullptr;
+          if (a.term_obs) dst = a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[t] : (size_t)e) * RL;
+        }
+        if (dst) {
+          fence_async_smem();
+          bulk_copy_rows(p, s.stage + (size_t)t * p.stage_stride, s.zeros, dst);
+          bulk_commit();
+        }
+      }
     }
     const unsigned m = __ballot_sync(0xffffffffu, fin);
     if (fin) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
@@ -612,7 +664,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
 
   // ---------------- phase 4 ----------------
   const int nd = s.misc[1];
-  {
+  if (!p.bulk_ok) {
     const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
     const size_t RL = (size_t)p.R * p.L;
     for (int g = warp; g < G; g += nwarp) {
@@ -629,8 +681,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   CHS_STAMP(11);
   // ---------------- phase 5 ----------------
   if (nd > 0) {
+    if (p.bulk_ok) bulk_wait_read();     // the staging area of finished envs is rebuilt below
     reset_envs<T>(a, s, e0, nd);
   }
+  if (p.bulk_ok) bulk_wait_read();       // shared memory must outlive the pending bulk reads
   CHS_STAMP(12);
 #undef CHS_STAMP
 }

@@ -38,6 +38,8 @@ struct KParams {
   int aero_flags;        // bit0 drag, bit1 ground effect, bit2 downwash (chs_drone.cuh: dyn_substeps_aero)
   int cp_ok;             // herd rows can be staged with 16-byte cp.async (alignment of row segments)
   int act4_ok;           // A == 4: one float4 load per action row
+  int bulk_ok;           // observations leave through bulk (TMA) stores: R*L*4 and the staging stride are multiples of 16 B
+  int zero_bytes;        // size of the shared zero block = R*L*4 - min(stage_stride*4, R*L*4)
   uint32_t seed_lo, seed_hi;
 };
 
@@ -72,10 +74,10 @@ template <typename T> struct KArgs {
 
 // ---- shared-memory carve-up (per CTA of G envs) ----------------------------------------------------
 struct SmemLayout {
-  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_ccent, off_ctab, off_int, total;
+  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_ccent, off_ctab, off_zero, off_int, total;
 };
 
-template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, int M, int G, int stage_stride) {
+template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, int M, int G, int stage_stride, int zero_bytes) {
   SmemLayout s;
   int o = 0;
   const int v4 = 4 * (int)sizeof(T), v2 = 2 * (int)sizeof(T);
@@ -89,6 +91,7 @@ template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, i
   s.off_stage = o; o += G * stage_stride * 4;
   s.off_ccent = o; o += G * 16;
   s.off_ctab = o; o += 152 * 8;         // CHS_TAB_DOUBLES (149) rounded up
+  s.off_zero = o; o += zero_bytes;      // multiple of 16
   s.off_int = o;  o += (10 * 32 + 8) * 4;  // ten per-env int arrays [32] + misc
   s.total = o;
   return s;

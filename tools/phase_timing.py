@@ -29,7 +29,8 @@ acc = np.zeros(12)
 tot = 0.0
 R = 20
 for i in range(R):
-    flush.zero_()
+    if not os.environ.get("NO_FLUSH"):
+        flush.zero_()
     env.step(acts[i % 8])
     torch.cuda.synchronize()
     c = clk.cpu().numpy().astype(np.float64)
@@ -42,3 +43,5 @@ print(f"E={E} G={G} threads={TH} grid={grid}: mean cycles per phase (avg over CT
 for n, v in zip(names, acc / R):
     print(f"  {n:18s} {v:9.0f} cyc")
 print(f"  sum {acc.sum() / R:.0f} cyc")
+c = clk.cpu().numpy().astype(np.float64)
+print("  last step, p3 detail: barrier->loop %.0f, loop %.0f, after loop->stamp7 %.0f" % ((c[:, 13] - c[:, 6]).mean(), (c[:, 14] - c[:, 13]).mean(), (c[:, 7] - c[:, 14]).mean()))
