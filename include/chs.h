@@ -87,7 +87,7 @@ typedef struct ChsParams {
   int32_t env_id_offset;      /* global id of local env 0 (multi-GPU sharding by env index) */
   int32_t envs_per_block;     /* launch tuning, 0 = auto */
   int32_t threads_per_block;  /* launch tuning, 0 = auto */
-  int32_t reserved0;
+  int32_t reserved0;          /* step mode at creation: 0 auto, 1 fused, 2 split (see chs_set_step_mode) */
   uint64_t seed;              /* Philox key; streams are keyed by (seed, global env id, episode) */
 } ChsParams;
 
@@ -182,6 +182,12 @@ int chs_set_debug_buffers(ChsHandle* h, int32_t* neighbors_dev, int32_t* herded_
  * about one wave), 2 = occupancy (64 registers, 4 CTAs of 256 threads per SM, for large batches); 0 = chosen
  * by grid size at every launch (default). */
 int chs_set_register_variant(ChsHandle* h, int32_t variant);
+
+/* How chs_step maps onto kernels: 1 = fused, one launch per control step (drone chains on the first warps of every
+ * CTA, the herd on the others: the shortest path for batches of about one wave); 2 = split, two launches
+ * (drone_kernel: one thread per drone, no shared memory, no barrier; step_kernel: herd, task layer, observation);
+ * 0 = chosen by batch size (default).  Results are bit-identical between the modes. */
+int chs_set_step_mode(ChsHandle* h, int32_t mode);
 
 /* Profiling aid: when non-NULL, thread 0 of every CTA of chs_step writes clock64() at the 7 phase boundaries
  * of the fused kernel into int64 [grid][16] (13 stamps used) (grid = ceil(E / envs_per_block)).  NULL disables. */

@@ -18,7 +18,7 @@ STAT_NAMES = ("episodes", "sum_return", "sum_length", "terminated", "trunc_altit
 # every symbol include/chs.h declares (checked by tests/test_abi.py)
 SYMBOLS = ("chs_abi_version", "chs_last_error", "chs_create", "chs_destroy", "chs_get_dims", "chs_set_spawn_table",
            "chs_reset", "chs_step", "chs_step_host", "chs_reset_host", "chs_get_state", "chs_set_state",
-           "chs_set_debug_buffers", "chs_set_phase_clock", "chs_set_register_variant", "chs_stats", "chs_set_launch")
+           "chs_set_debug_buffers", "chs_set_phase_clock", "chs_set_step_mode", "chs_set_register_variant", "chs_stats", "chs_set_launch")
 
 
 class ChsParams(C.Structure):
@@ -27,7 +27,7 @@ class ChsParams(C.Structure):
                 ("act_type", C.c_int32), ("start_level", C.c_int32), ("obs_rows", C.c_int32),
                 ("packing", C.c_int32), ("precision", C.c_int32), ("auto_reset", C.c_int32),
                 ("aero_flags", C.c_int32), ("cattle_integrate", C.c_int32), ("env_id_offset", C.c_int32),
-                ("envs_per_block", C.c_int32), ("threads_per_block", C.c_int32), ("reserved0", C.c_int32),
+                ("envs_per_block", C.c_int32), ("threads_per_block", C.c_int32), ("step_mode", C.c_int32),
                 ("seed", C.c_uint64)]
 
 
@@ -76,6 +76,7 @@ def load():
     lib.chs_set_debug_buffers.argtypes = [vp, vp, vp]
     lib.chs_set_phase_clock.argtypes = [vp, vp]
     lib.chs_set_register_variant.argtypes = [vp, i32]
+    lib.chs_set_step_mode.argtypes = [vp, i32]
     lib.chs_stats.argtypes = [vp, vp, i32]
     lib.chs_set_launch.argtypes = [vp, i32, i32]
     for s in SYMBOLS:

@@ -42,7 +42,7 @@ class CattleHerdingBatchedEnv:
     def __init__(self, num_envs, num_drones=3, num_cattle=20, pyb_freq=240, ctrl_freq=30, act="vel",
                  start_level=7, fixed_num_drones=0, obs_rows=None, auto_reset=True, precision="fp32",
                  spawn_table=None, device=None, env_id_offset=0, seed=0, envs_per_block=0, threads_per_block=0,
-                 packing="ctde", aero=0, cattle_integrate=False):
+                 packing="ctde", aero=0, cattle_integrate=False, step_mode="auto"):
         if not torch.cuda.is_available():
             raise RuntimeError("CattleHerdingBatchedEnv needs a CUDA device (there is no CPU fallback)")
         self.lib = _lib.load()
@@ -54,6 +54,7 @@ class CattleHerdingBatchedEnv:
         p.num_cattle, p.max_drones, p.fixed_num_drones = int(num_cattle), int(num_drones), int(fixed_num_drones)
         p.pyb_freq, p.ctrl_freq, p.act_type, p.start_level = int(pyb_freq), int(ctrl_freq), act_code, int(start_level)
         self.packing = packing
+        p.step_mode = {"auto": 0, "fused": 1, "split": 2}[step_mode]
         if not isinstance(aero, int):       # names -> ChsParams.aero_flags bits
             aero = sum({"drag": 1, "ground_effect": 2, "downwash": 4}[str(x)] for x in aero)
         p.aero_flags, p.cattle_integrate = int(aero), int(bool(cattle_integrate))
@@ -107,6 +108,10 @@ class CattleHerdingBatchedEnv:
         d = _lib.ChsDims()
         _lib.check(self.lib.chs_get_dims(self._h, C.byref(d)))
         return {n: getattr(d, n) for n, _ in d._fields_}
+
+    def set_step_mode(self, mode):
+        """"fused": one kernel per control step; "split": drone_kernel + step_kernel; "auto": by batch size."""
+        _lib.check(self.lib.chs_set_step_mode(self._h, {"auto": 0, "fused": 1, "split": 2}[mode]))
 
     def set_launch(self, envs_per_block, threads_per_block):
         _lib.check(self.lib.chs_set_launch(self._h, int(envs_per_block), int(threads_per_block)))

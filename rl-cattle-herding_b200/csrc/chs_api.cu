@@ -42,6 +42,9 @@ struct ChsHandle {
   int4 *envi, *envj;
   double* stats;
   double* tab;
+  void* own2;
+  void* pos0;
+  int step_mode;      // 0 auto, 1 fused (one kernel), 2 split (drone_kernel + step_kernel)
   int *dbg_nb, *dbg_herd;
   long long* dbg_clock;
   int threads, smem;
@@ -92,17 +95,20 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
   // different shared-memory needs can coexist (the launch's own size decides occupancy)
   if (smem > kSmemCap) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
   DeviceGuard dg(h->device);
+#define CHS_SMEM_ATTR(K) CUDA_TRY(cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap))
+#define CHS_SMEM_ATTR4(TT, MT, MB, FL)                                                                  \
+  CHS_SMEM_ATTR((step_kernel<TT, MT, MB, false, false, FL>)); CHS_SMEM_ATTR((step_kernel<TT, MT, MB, true, false, FL>)); \
+  CHS_SMEM_ATTR((step_kernel<TT, MT, MB, false, true, FL>));  CHS_SMEM_ATTR((step_kernel<TT, MT, MB, true, true, FL>))
   if (h->f64) {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<double, 512, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
-    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CHS_SMEM_ATTR4(double, 512, 1, true);
+    CHS_SMEM_ATTR(reset_kernel<double>);
   } else {
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 512, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
-    CUDA_TRY(cudaFuncSetAttribute(step_kernel<float, 256, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
-    CUDA_TRY(cudaFuncSetAttribute(reset_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemCap));
+    CHS_SMEM_ATTR4(float, 512, 1, true); CHS_SMEM_ATTR4(float, 256, 4, true);
+    CHS_SMEM_ATTR4(float, 512, 1, false); CHS_SMEM_ATTR4(float, 256, 4, false);
+    CHS_SMEM_ATTR(reset_kernel<float>);
   }
+#undef CHS_SMEM_ATTR4
+#undef CHS_SMEM_ATTR
   h->kp.G = G;
   h->kp.cp_ok = h->f64 ? 1 : ((G >= 2 && (h->E & 1) == 0) ? 1 : 0);
   h->threads = threads;
@@ -177,6 +183,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
     const int total = kp.R * kp.L * 4, c1 = kp.stage_stride * 4 < total ? kp.stage_stride * 4 : total;
     kp.zero_bytes = kp.bulk_ok ? total - c1 : 0;
   }
+  h->step_mode = prm->reserved0;
+  kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
   kp.aero_flags = prm->aero_flags;
   kp.act4_ok = (A == 4) ? 1 : 0;
@@ -198,6 +206,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   ALLOC0(h->envj, E * sizeof(int4));
   ALLOC0(h->stats, CHS_NUM_STATS * sizeof(double));
   ALLOC0(h->tab, 152 * sizeof(double));
+  ALLOC0(h->own2, D * E * 4 * ts);
+  if (prm->aero_flags & 4) { ALLOC0(h->pos0, D * E * 4 * ts); }
 #undef ALLOC0
   if (err != cudaSuccess) {
     chs_destroy(h);
@@ -237,7 +247,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
 extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
-  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab,
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0,
                   h->d_actions, h->d_obs, h->d_reward, h->d_termobs, h->d_term, h->d_trunc, h->d_mask, h->d_count, h->d_idx};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_count) cudaFreeHost(h->h_count);
@@ -290,6 +300,13 @@ extern "C" int chs_set_register_variant(ChsHandle* h, int32_t variant) {
   return CHS_OK;
 }
 
+extern "C" int chs_set_step_mode(ChsHandle* h, int32_t mode) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  if (mode < 0 || mode > 2) return fail(CHS_ERR_INVALID, "mode must be 0 (auto), 1 (fused) or 2 (split)");
+  h->step_mode = mode;
+  return CHS_OK;
+}
+
 extern "C" int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev) {
   if (!h) return fail(CHS_ERR_INVALID, "null handle");
   h->dbg_clock = (long long*)clock_dev;
@@ -310,6 +327,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
   a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats; a.tab = h->tab;
+  a.own2 = (typename VT<T>::v4*)h->own2; a.pos0 = (const typename VT<T>::v4*)h->pos0;
   a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd; a.dbg_clock = h->dbg_clock;
   return a;
 }
@@ -336,22 +354,27 @@ extern "C" int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_d
 }
 
 template <typename T> static void launch_step_variant(ChsHandle* h, const KArgs<T>& a, int grid, cudaStream_t st);
+#define CHS_LAUNCH(TT, MT, MB, FL)                                                                                 \
+  do {                                                                                                               \
+    if (marl) { if (split) step_kernel<TT, MT, MB, true, true, FL><<<grid, h->threads, h->smem, st>>>(a);            \
+                else step_kernel<TT, MT, MB, true, false, FL><<<grid, h->threads, h->smem, st>>>(a); }               \
+    else      { if (split) step_kernel<TT, MT, MB, false, true, FL><<<grid, h->threads, h->smem, st>>>(a);           \
+                else step_kernel<TT, MT, MB, false, false, FL><<<grid, h->threads, h->smem, st>>>(a); }              \
+  } while (0)
 template <> void launch_step_variant<double>(ChsHandle* h, const KArgs<double>& a, int grid, cudaStream_t st) {
-  if (h->kp.packing == CHS_PACK_MARL) step_kernel<double, 512, 1, true><<<grid, h->threads, h->smem, st>>>(a);
-  else step_kernel<double, 512, 1, false><<<grid, h->threads, h->smem, st>>>(a);
+  const bool marl = h->kp.packing == CHS_PACK_MARL, split = a.p.split != 0;
+  CHS_LAUNCH(double, 512, 1, true);
 }
 template <> void launch_step_variant<float>(ChsHandle* h, const KArgs<float>& a, int grid, cudaStream_t st) {
   // latency variant while the grid is under ~512 threads per SM, occupancy variant beyond
   const bool big = (h->reg_variant == 2 && h->threads <= 256) || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
-  const bool marl = h->kp.packing == CHS_PACK_MARL;
-  if (big) {
-    if (marl) step_kernel<float, 256, 4, true><<<grid, h->threads, h->smem, st>>>(a);
-    else step_kernel<float, 256, 4, false><<<grid, h->threads, h->smem, st>>>(a);
-  } else {
-    if (marl) step_kernel<float, 512, 1, true><<<grid, h->threads, h->smem, st>>>(a);
-    else step_kernel<float, 512, 1, false><<<grid, h->threads, h->smem, st>>>(a);
-  }
+  const bool marl = h->kp.packing == CHS_PACK_MARL, split = a.p.split != 0;
+  // lean build unless a runtime-checked feature is in use
+  const bool full = a.p.aero_flags || a.p.cattle_integrate || !a.p.cp_ok || !a.p.bulk_ok || a.dbg_clock || getenv("CHS_FULL_KERNEL");
+  if (full) { if (big) CHS_LAUNCH(float, 256, 4, true); else CHS_LAUNCH(float, 512, 1, true); }
+  else      { if (big) CHS_LAUNCH(float, 256, 4, false); else CHS_LAUNCH(float, 512, 1, false); }
 }
+#undef CHS_LAUNCH
 
 template <typename T>
 static int launch_step(ChsHandle* h, const float* actions, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
@@ -360,6 +383,14 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   a.actions = actions; a.obs = obs; a.reward = reward; a.terminated = term; a.truncated = trunc;
   a.term_obs = term_obs; a.term_mode = term_obs ? term_mode : 0; a.term_count = term_count; a.term_idx = term_idx;
   const int grid = (h->E + h->kp.G - 1) / h->kp.G;
+  // split mode: the drones get their own barrier-free kernel; auto picks it once the batch is several waves deep
+  const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 2048);
+  if (split) {
+    if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
+    const long long nthr = (long long)h->kp.D * h->E;
+    drone_kernel<T><<<(unsigned)((nthr + 255) / 256), 256, 0, st>>>(a);
+    a.p.split = 1;
+  }
   launch_step_variant<T>(h, a, grid, st);
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;

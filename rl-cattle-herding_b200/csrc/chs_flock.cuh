@@ -88,7 +88,14 @@ __device__ __forceinline__ typename VT<T>::v2 herd_finish(const typename VT<T>::
       const T ap = ax * pi.x + ay * pi.y;
       const T pikx = mu * (pi.x - ax * ap), piky = mu * (pi.y - ay * ap);   // mu * (I - a a^T) p_i
       const T om = T(1) - mu;                                 // q_ik - q_i = (1-mu)(y_k - q_i)
-      lattice_term<T>(-om * ex, -om * ey, pikx - pi.x, piky - pi.y, T(k::SIGMA_BETA), T(1.0 / k::SIGMA_BETA), gx, gy, cx, cy);
+      if (om == T(0)) {
+        // drone farther than the shepherd radius (the usual case): the projected point coincides with the cow,
+        // sigma_norm = 0, bump = 1 and the gradient weight multiplies a zero displacement -- lattice_term would add
+        // exactly (0, 0) to the gradient and 1 * (p_ik - p_i) to the consensus
+        cx += pikx - pi.x; cy += piky - pi.y;
+      } else {
+        lattice_term<T>(-om * ex, -om * ey, pikx - pi.x, piky - pi.y, T(k::SIGMA_BETA), T(1.0 / k::SIGMA_BETA), gx, gy, cx, cy);
+      }
       if (r <= T(k::DANGER_RANGE)) {                          // -k (y_k - q_i)/|.|^3 ; r == 0 -> NaN like numpy
         const T inv = T(k::PREDATOR_K) * Mth<T>::frcp(r * r * r);
         px += inv * ex; py += inv * ey;

@@ -125,7 +125,7 @@ __device__ __forceinline__ int draw_num_drones(const KParams& p, int gid, int ep
 // first observation (BaseAviary.reset :280-331, _housekeeping :547-637, initialize_drone_positions
 // :251-277).  PID state, prev_cent_dist, the spacing clock and the curriculum survive.
 // Must be called by every thread of the CTA; `nd` is CTA-uniform.
-template <typename T>
+template <typename T, bool FULL>
 __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0, int nd) {
   const KParams& p = a.p;
   const int t = threadIdx.x, nt = blockDim.x, G = p.G, E = p.E;
@@ -183,7 +183,7 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
     }
   }
   __syncthreads();
-  if (a.obs && p.bulk_ok) {
+  if (a.obs && (!FULL || p.bulk_ok)) {
     if (t < nd) {
       const int g = s.dlist[t];
       fence_async_smem();
@@ -191,7 +191,7 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
       bulk_commit();
       bulk_wait_read();
     }
-  } else if (a.obs) {
+  } else if (FULL && a.obs) {
     const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
     for (int i = warp; i < nd; i += nwarp) {
       const int g = s.dlist[i];
@@ -229,14 +229,61 @@ __global__ void __launch_bounds__(512) reset_kernel(const KArgs<T> a) {
   }
   __syncthreads();
   const int nd = s.misc[1];
-  if (nd > 0) reset_envs<T>(a, s, e0, nd);
+  if (nd > 0) reset_envs<T, true>(a, s, e0, nd);
+}
+
+// Split mode, kernel 1 of 2: one thread per (drone slot, env), env index fastest.  action -> PID -> K DYN substeps in
+// registers with no shared memory and no barrier, so the long dependent chain of every drone is hidden by plain
+// occupancy; writes the drone state, the RPMs and the (ang_v, yaw) scratch row the second kernel needs for the
+// observation.  The fused kernel below does the same work on its "drone" threads (phase 1).
+template <typename T>
+__global__ void __launch_bounds__(256) drone_kernel(const KArgs<T> a) {
+  const KParams& p = a.p;
+  const int E = p.E, D = p.D;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)D * E) return;
+  const int d = (int)(idx / E), e = (int)(idx - (long long)d * E);
+  const int n = a.envi[e].z;
+  if (d >= n) return;
+  const T ctrl_dt = T(1.0) / T(p.ctrl_freq);
+  const T pyb_dt = T(1.0) / T(p.ctrl_freq * p.K);
+  DroneState<T> ds;
+  load_drone<T>(a, d, e, ds);
+  float act[4] = {0.f, 0.f, 0.f, 0.f};
+  const float* ap = a.actions + ((size_t)e * D + d) * p.A;
+  if (p.A == 4 && p.act4_ok) {
+    const float4 v = *reinterpret_cast<const float4*>(ap);
+    act[0] = v.x; act[1] = v.y; act[2] = v.z; act[3] = v.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (i < p.A) act[i] = ap[i];
+  }
+  T rpm[4];
+  action_to_rpm<T>(p, ds, act, ctrl_dt, rpm);
+  if (p.aero_flags) {
+    const auto pr = a.rpm[(size_t)d * E + e];
+    const T prev[4] = {pr.x, pr.y, pr.z, pr.w};
+    DroneState<T> tmp = ds;
+    T rp[4] = {rpm[0], rpm[1], rpm[2], rpm[3]};
+    dyn_substeps_aero<T>(tmp, rp, prev, p.K, pyb_dt, p.aero_flags, a.pos0 + e, E, n, d);
+    ds = tmp;
+  } else {
+    dyn_substeps<T>(ds, rpm, p.K, pyb_dt);
+  }
+  store_drone<T>(a, d, e, ds);
+  a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
+  a.own2[(size_t)d * E + e] = mk4<T>(ds.av[0], ds.av[1], ds.av[2], ds.rpy[2]);
 }
 
 // Two register budgets are compiled: MINB = 1 (up to 128 registers per thread, shortest dependent chains, for
 // grids of about one wave where latency decides) and MINB = 4 (64 registers, 4 CTAs of 256 threads per SM, for
 // large batches where issue-slot occupancy decides).  The host picks by grid size.
 // MARL selects the rllib_envs packing (per-drone reward / flags, sequential reward loop) at compile time.
-template <typename T, int MAXT, int MINB, bool MARL>
+// SPLIT drops the drone chain (drone_kernel ran it) at compile time: fewer registers, a smaller kernel.
+// FULL = false is the lean build for the common configuration (no aero extras, no kinematic herd, async herd staging
+// and bulk obs stores usable, no phase stamps): those branches are compiled out, which matters for batches of about
+// one wave where the kernel is bound by cold instruction fetch (tools/microbench/icache_cold.cu).
+template <typename T, int MAXT, int MINB, bool MARL, bool SPLIT, bool FULL>
 __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const KParams& p = a.p;
@@ -250,7 +297,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   int ndt = (DG + 31) & ~31;          // "drone" threads: the first warps of the CTA
   if (ndt > nt) ndt = nt;
 
-#define CHS_STAMP(i) do { if (a.dbg_clock && t == 0) a.dbg_clock[(size_t)blockIdx.x * 16 + (i)] = clock64(); } while (0)
+#define CHS_STAMP(i) do { if (FULL && a.dbg_clock && t == 0) a.dbg_clock[(size_t)blockIdx.x * 16 + (i)] = clock64(); } while (0)
   CHS_STAMP(0);
   // ---------------- phase 0 ----------------
   // Every global read the step needs is issued here, before the first barrier, so that the DRAM round trips
@@ -266,8 +313,15 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   }
   DroneState<T> ds0;
   float act0[4] = {0.f, 0.f, 0.f, 0.f};
+  typename VT<T>::v4 sp0 = mk4<T>(0, 0, 0, 0), sp1 = sp0, sp2 = sp0;     // split mode: fields A, C and the own2 row
   const bool have0 = (t < ndt) && (t < DG) && (e0 + (t & (G - 1)) < E);
-  if (have0) {
+  if constexpr (SPLIT) {
+    if (have0) {
+      const int g = t & (G - 1), d = t >> lg, e = e0 + g;
+      const size_t st = (size_t)D * E, o = (size_t)d * E + e;
+      sp0 = a.drone[F_A * st + o]; sp1 = a.drone[F_C * st + o]; sp2 = a.own2[o];
+    }
+  } else if (have0) {
     const int g = t & (G - 1), d = t >> lg, e = e0 + g;
     load_drone<T>(a, d, e, ds0);
     const float* ap = a.actions + ((size_t)e * D + d) * p.A;
@@ -281,7 +335,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   }
   {
     using V2 = typename VT<T>::v2;
-    if (p.cp_ok) {
+    if (!FULL || p.cp_ok) {
       // herd rows -> shared memory as 16-byte asynchronous copies (no register staging, all in flight at once);
       // envs past the end of the batch are zero-filled through the src-size operand
       constexpr int EPC = 16 / (int)sizeof(V2);            // envs per 16-byte chunk
@@ -298,7 +352,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         cp_async16(dst, src, valid * (int)sizeof(V2));
       }
     }
-    if (p.aero_flags & 4) {   // downwash: start-of-step positions of every drone, parked in redA until phase 2
+    if (FULL && (p.aero_flags & 4) && !SPLIT) {   // downwash: start-of-step positions of every drone, parked in redA until phase 2
       const size_t st = (size_t)D * E;
       for (int it = t; it < DG; it += nt) {
         const int g = it & (G - 1), d = it >> lg, e = e0 + g;
@@ -312,7 +366,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     float4* st4 = reinterpret_cast<float4*>(s.stage);
     for (int i = t; i < nq; i += nt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int i = t; i < (p.zero_bytes >> 4); i += nt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (!p.cp_ok) {
+    if (FULL && !p.cp_ok) {
       for (int it = t; it < M * G; it += nt) {
         const int g = it & (G - 1), j = it >> lg, e = e0 + g;
         if (e < E) { s.cpos[it] = a.cpos[(size_t)j * E + e]; s.cvel[it] = a.cvel[(size_t)j * E + e]; }
@@ -338,7 +392,26 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
 
   // ---------------- phase 1 ----------------
   const int nact = s.misc[0];
-  if (t < ndt) {
+  if constexpr (SPLIT) {
+    // the drones were integrated by drone_kernel: stage their positions and the own-state part of the obs rows
+    if (t < ndt) {
+      for (int it = t; it < DG; it += ndt) {
+        const int g = it & (G - 1), d = it >> lg, e = e0 + g;
+        if (e < E && d < s.n[g]) {
+          typename VT<T>::v4 A = sp0, C = sp1, O = sp2;
+          if (it != t) {
+            const size_t st = (size_t)D * E, o = (size_t)d * E + e;
+            A = a.drone[F_A * st + o]; C = a.drone[F_C * st + o]; O = a.own2[o];
+          }
+          s.dpos[it] = mk4<T>(A.x, A.y, A.z, T(0));
+          float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
+          row[0] = (float)A.z; row[1] = (float)A.w; row[2] = (float)C.w; row[3] = (float)O.w;
+          row[4] = (float)C.x; row[5] = (float)C.y; row[6] = (float)C.z;
+          row[7] = (float)O.x; row[8] = (float)O.y; row[9] = (float)O.z;
+        }
+      }
+    }
+  } else if (t < ndt) {
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       if (e < E && d < s.n[g]) {
@@ -356,7 +429,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         }
         T rpm[4];
         action_to_rpm<T>(p, ds, act, ctrl_dt, rpm);
-        if (p.aero_flags) {
+        if (FULL && p.aero_flags) {
           const auto pr = a.rpm[(size_t)d * E + e];
           const T prev[4] = {pr.x, pr.y, pr.z, pr.w};
           DroneState<T> tmp = ds;      // the out-of-line call takes an address: keep `ds` itself in registers
@@ -380,7 +453,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   {
     // worker threads (everyone when the CTA has no spare warps): herd centroid per env in float64, then the
     // alpha-lattice term of the herds that update this step -- neither depends on the drones
-    const int wt0 = (ndt < nt) ? ndt : 0;
+    const int wt0 = (ndt < nt && !SPLIT) ? ndt : 0;
     const int nw = nt - wt0;
     if (t >= wt0) {
       const int w = t - wt0;
@@ -406,7 +479,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   // ---------------- phase 2 ----------------
   // per-drone pieces: neighbour ranking + spacing rewards on the drone threads, cattle pieces on threads half a
   // CTA away so that the two halves run on different warps
-  if (p.cattle_integrate) {
+  if (FULL && p.cattle_integrate) {
     // non-reference kinematic herd: velocities first, then pos += vel * CTRL_TIMESTEP for
     // every cow of every env, then the herd centroid again; obs / reward / effectiveness below see the new positions
     for (int it = t; it < nact * M; it += nt) {
@@ -452,7 +525,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       if (e < E && d < s.n[g]) drone_cattle<T>(p, g, d, true, s.dpos, s.cpos, s.redB, s.stage);
     }
   }
-  if (!p.cattle_integrate) {
+  if (!FULL || !p.cattle_integrate) {
     for (int it = t; it < nact * M; it += nt) {
       const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
       const auto ua = s.u[i * G + g];
@@ -639,7 +712,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       a.envj[e] = ej;
       a.envf[e] = ef;
       a.epret[e] = epret;
-      if (p.bulk_ok) {
+      if (!FULL || p.bulk_ok) {
         // phase 4 folded in: this thread knows where its env's observation goes and ships it with two bulk stores
         const size_t RL = (size_t)p.R * p.L;
         float* dst = a.obs ? a.obs + (size_t)e * RL : nullptr;
@@ -664,7 +737,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
 
   // ---------------- phase 4 ----------------
   const int nd = s.misc[1];
-  if (!p.bulk_ok) {
+  if (FULL && !p.bulk_ok) {
     const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
     const size_t RL = (size_t)p.R * p.L;
     for (int g = warp; g < G; g += nwarp) {
@@ -681,10 +754,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   CHS_STAMP(11);
   // ---------------- phase 5 ----------------
   if (nd > 0) {
-    if (p.bulk_ok) bulk_wait_read();     // the staging area of finished envs is rebuilt below
-    reset_envs<T>(a, s, e0, nd);
+    if (!FULL || p.bulk_ok) bulk_wait_read();     // the staging area of finished envs is rebuilt below
+    reset_envs<T, FULL>(a, s, e0, nd);
   }
-  if (p.bulk_ok) bulk_wait_read();       // shared memory must outlive the pending bulk reads
+  if (!FULL || p.bulk_ok) bulk_wait_read();       // shared memory must outlive the pending bulk reads
   CHS_STAMP(12);
 #undef CHS_STAMP
 }

@@ -38,6 +38,7 @@ struct KParams {
   int aero_flags;        // bit0 drag, bit1 ground effect, bit2 downwash (chs_drone.cuh: dyn_substeps_aero)
   int cp_ok;             // herd rows can be staged with 16-byte cp.async (alignment of row segments)
   int act4_ok;           // A == 4: one float4 load per action row
+  int split;             // 1: drones are integrated by drone_kernel, step_kernel does the rest
   int bulk_ok;           // observations leave through bulk (TMA) stores: R*L*4 and the staging stride are multiples of 16 B
   int zero_bytes;        // size of the shared zero block = R*L*4 - min(stage_stride*4, R*L*4)
   uint32_t seed_lo, seed_hi;
@@ -49,6 +50,8 @@ template <typename T> struct KArgs {
   typename VT<T>::v4* rpm;
   typename VT<T>::v2* cpos;
   typename VT<T>::v2* cvel;
+  typename VT<T>::v4* own2;           // split mode scratch [D][E]: (ang_v, yaw) of the step
+  const typename VT<T>::v4* pos0;     // split mode + downwash: start-of-step copy of drone field A [D][E]
   int4* envi;
   int4* envj;
   double2* envf;

@@ -174,6 +174,33 @@ def test_register_variants_agree():
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("kw", [dict(), dict(aero=7), dict(packing="marl", num_drones=4, fixed_num_drones=4, start_level=2),
+                                dict(num_drones=12, fixed_num_drones=0, num_cattle=16, start_level=7)])
+def test_split_mode_equals_fused_mode(kw):
+    """drone_kernel + step_kernel == the fused kernel (same device functions; fp32 may differ by FMA contraction
+    between the two compilations, fp64 and every integer / flag must agree exactly over auto-resets)."""
+    for precision in ("fp64", "fp32"):
+        E = 200
+        a, _ = _make(E, precision=precision, step_mode="fused", **dict(kw))
+        b, _ = _make(E, precision=precision, step_mode="split", **dict(kw))
+        a.reset(); b.reset()
+        D = a.max_drones
+        gen = torch.Generator("cuda").manual_seed(5)
+        for t in range(30):
+            act = torch.rand((E, D, 4), device="cuda", generator=gen) * 2 - 1
+            oa, ra, ta, ua = a.step(act)
+            ob, rb, tb, ub = b.step(act)
+            assert torch.equal(ta, tb) and torch.equal(ua, ub), (precision, t)
+            tol = 0.0 if precision == "fp64" else 2e-6
+            assert (oa - ob).abs().max().item() <= tol and (ra - rb).abs().max().item() <= tol * 10, (precision, t)
+            if precision == "fp32":      # keep the twins on the same trajectory: the roll loop amplifies 1-ulp differences
+                b.set_state(a.get_state())
+        sa, sb = a.get_state(), b.get_state()
+        for k in ("n_drones", "level", "tally", "episode", "step_counter"):
+            assert np.array_equal(sa[k], sb[k]), (precision, k)
+        a.close(); b.close()
+
+
 def test_error_paths():
     pkg = _pkg()
     env = pkg.CattleHerdingBatchedEnv(4, num_drones=3, num_cattle=20, device=0)

@@ -33,22 +33,26 @@ def main():
         acts = [torch.rand((E, D, 4), device="cuda") * 2 - 1 for _ in range(4)]
         flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if E * 4230 < (200 << 20) else None
         res = []
-        for g in (2, 4, 8, 16, 32):
-            for th in (32, 64, 96, 128, 256, 512):
-                for var in (1, 2):
-                    if var == 2 and th > 256:
-                        continue
-                    try:
-                        env.set_launch(g, th)
-                        pkg._lib.check(env.lib.chs_set_register_variant(env._h, var))
-                        ms = time_shape(env, acts, flush, 16 if E <= 65536 else 8)
-                        res.append((ms, g, th, var, env.dims["smem_bytes"]))
-                    except RuntimeError as ex:
-                        print("skip", g, th, var, str(ex)[:60])
+        for mode in ("fused", "split"):
+            env.set_step_mode(mode)
+            for g in (4, 8, 16, 32):
+                for th in (64, 96, 128, 256, 512):
+                    for var in (1, 2):
+                        if var == 2 and th > 256:
+                            continue
+                        try:
+                            env.set_launch(g, th)
+                            pkg._lib.check(env.lib.chs_set_register_variant(env._h, var))
+                            ms = time_shape(env, acts, flush, 16 if E <= 65536 else 8)
+                            res.append((ms, g, th, var, mode))
+                        except RuntimeError as ex:
+                            print("skip", g, th, var, str(ex)[:60])
         res.sort()
         print(f"E={E} D={D} M={M}")
-        for ms, g, th, var, sm in res[:14]:
-            print(f"  {ms * 1e3:9.1f} us  G={g:2d} threads={th:3d} variant={var} smem={sm}")
+        for ms, g, th, var, sm in res[:12]:
+            print(f"  {ms * 1e3:9.1f} us  G={g:2d} threads={th:3d} variant={var} {sm}")
+        best_fused = min(r for r in res if r[4] == "fused")
+        print("  best fused:", round(best_fused[0] * 1e3, 1), best_fused[1:])
         print("  worst:", [(round(r[0] * 1e3, 1), r[1], r[2], r[3]) for r in res[-3:]])
         env.close()
 
