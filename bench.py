@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--cattle", type=int, default=20)
     ap.add_argument("--ctrl-freq", type=int, default=30)
     ap.add_argument("--launch", default="auto", help="'auto' or G,threads")
+    ap.add_argument("--step-mode", default="auto", choices=["auto", "fused", "split"],
+                    help="fused: one kernel per control step; split: drone_kernel + step_kernel; auto: the faster one (untimed probe)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
@@ -196,17 +198,21 @@ def time_steps(env, torch, action_pool, n_steps, flush_buf, stream_sync=True):
     return [s.elapsed_time(e) for s, e in zip(starts, ends)]   # ms each
 
 
-def autotune_launch(env, torch, action_pool, flush_buf, candidates, reps=12):
+def autotune_launch(env, torch, action_pool, flush_buf, candidates, reps=12, modes=("fused",)):
+    """Untimed: picks (envs per CTA, threads per CTA, step mode) by median step time.  Returns (ms, G, threads, mode)."""
     best = None
-    for g, th in candidates:
-        try:
-            env.set_launch(g, th)
-        except RuntimeError:
-            continue
-        time_steps(env, torch, action_pool, 3, flush_buf)
-        ms = float(np.median(time_steps(env, torch, action_pool, reps, flush_buf)))
-        if best is None or ms < best[0]:
-            best = (ms, g, th)
+    for mode in modes:
+        env.set_step_mode(mode)
+        for g, th in candidates:
+            try:
+                env.set_launch(g, th)
+            except RuntimeError:
+                continue
+            time_steps(env, torch, action_pool, 3, flush_buf)
+            ms = float(np.median(time_steps(env, torch, action_pool, reps, flush_buf)))
+            if best is None or ms < best[0]:
+                best = (ms, g, th, mode)
+    env.set_step_mode(best[3])
     env.set_launch(best[1], best[2])
     return best
 
@@ -239,12 +245,15 @@ def run_cuda_arm(args):
 
     # ---- warm-up + launch-shape selection (untimed) ----
     if args.launch == "auto":
-        cands = [(g, th) for g in (4, 8, 16, 32) for th in (128, 256)]
-        tuned = autotune_launch(env, torch, action_pool, flush_buf, cands)
+        cands = [(4, 64), (8, 96)] + [(g, th) for g in (4, 8, 16, 32) for th in (128, 256)]
+        tuned = autotune_launch(env, torch, action_pool, flush_buf, cands,
+                                modes=("fused", "split") if args.step_mode == "auto" else (args.step_mode,))
     else:
         g, th = (int(x) for x in args.launch.split(","))
+        mode = "fused" if args.step_mode == "auto" else args.step_mode
+        env.set_step_mode(mode)
         env.set_launch(g, th)
-        tuned = (None, g, th)
+        tuned = (None, g, th, mode)
     time_steps(env, torch, action_pool, W, flush_buf)
     env.stats(reset=True)
 
@@ -282,17 +291,19 @@ def run_cuda_arm(args):
             "config": {"workload": f"CattleAviary Physics.DYN, {N} drones + {M} cattle, {E} envs per GPU, VEL actions, "
                                    f"240 Hz physics / {args.ctrl_freq} Hz ctrl, level 7, uniform random actions, auto-reset",
                        "envs_per_gpu": E, "total_envs": world * E, "obs_shape": [dims["obs_rows"], dims["obs_len"]],
-                       "launch": {"envs_per_block": tuned[1], "threads_per_block": tuned[2], "smem_bytes": env.dims["smem_bytes"]},
+                       "launch": {"envs_per_block": tuned[1], "threads_per_block": tuned[2], "smem_bytes": env.dims["smem_bytes"],
+                                  "step_mode": tuned[3]},
                        "l2": "flushed between steps by zeroing a 256 MiB buffer (outside the per-step event pairs)",
                        "timing": "sum of per-launch CUDA-event durations on the launching stream, max over ranks",
                        "sharding": "env index, no collective on the step path; one NCCL all-reduce of the stats vector after the run"},
             "drone_steps_per_s": value * N,
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / K,
-            "gpu_launches": K,
+            "gpu_launches": K * (2 if tuned[3] == "split" else 1),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": recorded_traffic(wl_key), "bytes_per_env_step": bytes_env,
                          "bytes_per_launch": bytes_env * E, "peak_source": peak_src,
-                         "kernel": "chs::step_kernel<float>", "kernel_ms": float(np.mean(per_step_ms))},
+                         "kernel": "chs::step_kernel<float>" if tuned[3] == "fused" else "chs::drone_kernel<float> + chs::step_kernel<float> (one control step)",
+                         "kernel_ms": float(np.mean(per_step_ms))},
             "clocks": clocks.summary(),
             "episodes": {"finished": float(stats[0].item()), "mean_length": float(stats[2].item() / max(1.0, stats[0].item())),
                          "mean_return": float(stats[1].item() / max(1.0, stats[0].item())), "non_finite": float(stats[9].item())},
@@ -334,10 +345,11 @@ def run_cuda_arm(args):
             pool2 = [torch.rand((Es, N, 4), device=dev, generator=gen) * 2 - 1 for _ in range(4)]
             e2.reset()
             fb = flush_buf if Es * (bytes_env + 1200) < 200e6 else None
-            best = autotune_launch(e2, torch, pool2, fb, [(g, th) for g in (8, 16, 32) for th in (128, 256)], reps=6)
+            best = autotune_launch(e2, torch, pool2, fb, [(16, 64)] + [(g, th) for g in (16, 32) for th in (128, 256)], reps=6,
+                                   modes=("fused", "split"))
             ms = float(np.mean(time_steps(e2, torch, pool2, 30, fb)))
             sweep.append({"envs": Es, "ms_per_step": ms, "env_steps_per_s": Es / (ms * 1e-3),
-                          "hbm_frac": bytes_env * Es / (ms * 1e-3) / 1e9 / peak, "launch": [best[1], best[2]],
+                          "hbm_frac": bytes_env * Es / (ms * 1e-3) / 1e9 / peak, "launch": [best[1], best[2]], "step_mode": best[3],
                           "l2": "flushed" if fb is not None else "working set > L2"})
             e2.close()
             del pool2

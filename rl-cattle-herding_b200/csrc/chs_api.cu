@@ -384,7 +384,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   a.term_obs = term_obs; a.term_mode = term_obs ? term_mode : 0; a.term_count = term_count; a.term_idx = term_idx;
   const int grid = (h->E + h->kp.G - 1) / h->kp.G;
   // split mode: the drones get their own barrier-free kernel; auto picks it once the batch is several waves deep
-  const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 2048);
+  const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 1024);
   if (split) {
     if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
     const long long nthr = (long long)h->kp.D * h->E;

@@ -113,38 +113,39 @@ template <typename T>
 __device__ __forceinline__ void action_to_rpm(const KParams& p, DroneState<T>& s, const float* __restrict__ act,
                                               T ctrl_dt, T rpm[4]) {
   const T cf = T(p.ctrl_freq);
+  // every PID-driven action type reduces to (target position, target yaw, target velocity): one dsl_pid call site
+  bool pid = true;
+  T tp[3] = {s.p[0], s.p[1], s.p[2]}, tv[3] = {T(0), T(0), T(0)}, tyaw = T(0);
   if (p.act == 0) {            // VEL (:185-222)
     const float a0 = act[0], a1 = act[1], a3 = act[3];
     const float nrm = __fsqrt_rn(__fadd_rn(__fmul_rn(a0, a0), __fmul_rn(a1, a1)));
     float ux = 0.f, uy = 0.f;
     if (nrm != 0.f) { ux = __fdiv_rn(a0, nrm); uy = __fdiv_rn(a1, nrm); }
     const float scale = __fmul_rn(2.5f, fabsf(a3));
-    const T tv[3] = {T(ux) * T(scale), T(uy) * T(scale), T(0)};
-    const T tp[3] = {s.p[0], s.p[1], T(k::TARGET_ALT)};
-    dsl_pid<T>(s, tp, s.rpy[2], tv, ctrl_dt, cf, rpm);
+    tv[0] = T(ux) * T(scale); tv[1] = T(uy) * T(scale);
+    tp[2] = T(k::TARGET_ALT);
+    tyaw = s.rpy[2];
   } else if (p.act == 1) {     // RPM (:168-169)
+    pid = false;
 #pragma unroll
     for (int i = 0; i < 4; ++i) rpm[i] = T(k::HOVER_RPM) * T(__fadd_rn(1.0f, __fmul_rn(0.05f, act[i])));
   } else if (p.act == 3) {     // ONE_D_RPM (:223-224)
+    pid = false;
     const T r = T(k::HOVER_RPM) * T(__fadd_rn(1.0f, __fmul_rn(0.05f, act[0])));
     rpm[0] = rpm[1] = rpm[2] = rpm[3] = r;
   } else if (p.act == 4) {     // ONE_D_PID (:225-234)
-    const T tp[3] = {s.p[0], s.p[1], s.p[2] + T(0.1) * T(act[0])};
-    const T tv[3] = {T(0), T(0), T(0)};
-    dsl_pid<T>(s, tp, T(0), tv, ctrl_dt, cf, rpm);
+    tp[2] = s.p[2] + T(0.1) * T(act[0]);
   } else {                     // PID waypoint through _calculateNextStep, step_size 1 (BaseAviary.py:1318-1348)
     const T wp[3] = {T(act[0]), T(act[1]), T(act[2])};
     const T d[3] = {wp[0] - s.p[0], wp[1] - s.p[1], wp[2] - s.p[2]};
     const T dist = Mth<T>::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
-    T tp[3];
     if (dist <= T(1)) { tp[0] = wp[0]; tp[1] = wp[1]; tp[2] = wp[2]; }
     else {
 #pragma unroll
       for (int i = 0; i < 3; ++i) tp[i] = s.p[i] + d[i] / dist;   // rare branch, exact
     }
-    const T tv[3] = {T(0), T(0), T(0)};
-    dsl_pid<T>(s, tp, T(0), tv, ctrl_dt, cf, rpm);
   }
+  if (pid) dsl_pid<T>(s, tp, tyaw, tv, ctrl_dt, cf, rpm);
 }
 
 // K substeps of BaseAviary._dynamics (:1043-1102) + _integrateQ (:1104-1117) with constant rpm.
