@@ -44,6 +44,8 @@ struct ChsHandle {
   double* tab;
   void* own2;
   void* pos0;
+  int* done_list;
+  int* done_count;
   int step_mode;      // 0 auto, 1 fused (one kernel), 2 split (drone_kernel + step_kernel)
   int *dbg_nb, *dbg_herd;
   long long* dbg_clock;
@@ -207,6 +209,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   ALLOC0(h->stats, CHS_NUM_STATS * sizeof(double));
   ALLOC0(h->tab, 152 * sizeof(double));
   ALLOC0(h->own2, D * E * 4 * ts);
+  ALLOC0(h->done_list, E * sizeof(int));
+  ALLOC0(h->done_count, sizeof(int));
   if (prm->aero_flags & 4) { ALLOC0(h->pos0, D * E * 4 * ts); }
 #undef ALLOC0
   if (err != cudaSuccess) {
@@ -247,7 +251,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
 extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
-  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0,
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count,
                   h->d_actions, h->d_obs, h->d_reward, h->d_termobs, h->d_term, h->d_trunc, h->d_mask, h->d_count, h->d_idx};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_count) cudaFreeHost(h->h_count);
@@ -338,7 +342,8 @@ template <typename T>
 static int launch_reset(ChsHandle* h, const uint8_t* mask_dev, float* obs_dev, cudaStream_t st) {
   KArgs<T> a = base_args<T>(h);
   a.reset_mask = mask_dev; a.obs = obs_dev;
-  const int grid = (h->E + h->kp.G - 1) / h->kp.G;
+  const int ngroups = (h->E + h->kp.G - 1) / h->kp.G;
+  const int grid = ngroups < 148 * 8 ? ngroups : 148 * 8;
   reset_kernel<T><<<grid, h->threads, h->smem, st>>>(a);
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;
@@ -388,10 +393,18 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   if (split) {
     if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
     const long long nthr = (long long)h->kp.D * h->E;
+    if (h->kp.auto_reset && !getenv("CHS_INLINE_RESET")) a.done_count = h->done_count;
     drone_kernel<T><<<(unsigned)((nthr + 255) / 256), 256, 0, st>>>(a);
     a.p.split = 1;
   }
+  const bool defer = split && h->kp.auto_reset && !getenv("CHS_INLINE_RESET");
+  if (defer) { a.done_list = h->done_list; a.done_count = h->done_count; }
   launch_step_variant<T>(h, a, grid, st);
+  if (defer) {
+    KArgs<T> r = base_args<T>(h);
+    r.done_list = h->done_list; r.done_count = h->done_count; r.obs = obs;
+    reset_list_kernel<T><<<148 * 4, 256, 0, st>>>(r);
+  }
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;
 }

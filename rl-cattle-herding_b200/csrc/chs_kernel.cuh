@@ -200,36 +200,161 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
   }
 }
 
+// Masked reset.  Persistent CTAs: each one scans the mask bytes of its groups of G consecutive envs at once (one
+// coalesced pass), keeps the groups that hold a selected env in a work list and resets only those -- the usual
+// case after a step is that most groups have nothing to do, and launching a CTA per group costs more than the work.
 template <typename T>
 __global__ void __launch_bounds__(512) reset_kernel(const KArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int work[256];
+  __shared__ int nwork;
   const KParams& p = a.p;
   Smem<T> s = carve<T>(smem_raw, p);
-  const int t = threadIdx.x, G = p.G, E = p.E;
-  const int e0 = blockIdx.x * G;
-  if (t < 32) {
-    bool sel = false;
-    const int e = e0 + t;
-    if (t < G && e < E && (a.reset_mask == nullptr || a.reset_mask[e])) {
-      sel = true;
-      int4 ei = a.envi[e];
+  const int t = threadIdx.x, nt = blockDim.x, G = p.G, E = p.E;
+  const int ngroups = (E + G - 1) / G;
+  const int per_cta = (ngroups + gridDim.x - 1) / gridDim.x;
+  for (int base = 0; base < per_cta; base += 256) {
+    if (t == 0) nwork = 0;
+    __syncthreads();
+    for (int k = t; k < 256 && base + k < per_cta; k += nt) {
+      const int grp = blockIdx.x + (base + k) * gridDim.x;       // interleaved: neighbouring CTAs read neighbouring bytes
+      if (grp < ngroups) {
+        bool any = (a.reset_mask == nullptr);
+        if (!any) {
+          const int eb = grp * G, en = (eb + G < E) ? eb + G : E;
+          for (int e = eb; e < en; ++e) any = any || (a.reset_mask[e] != 0);
+        }
+        if (any) work[atomicAdd(&nwork, 1)] = grp;               // processing order does not affect the results
+      }
+    }
+    __syncthreads();
+    const int nw = nwork;
+    for (int w = 0; w < nw; ++w) {
+      const int e0 = work[w] * G;
+      if (t < 32) {
+        bool sel = false;
+        const int e = e0 + t;
+        if (t < G && e < E && (a.reset_mask == nullptr || a.reset_mask[e])) {
+          sel = true;
+          int4 ei = a.envi[e];
+          int4 ej = a.envj[e];
+          ej.z += 1;                                         // episode index
+          const int n = draw_num_drones(p, p.env_id_offset + e, ej.z);
+          int row = ei.w + 1;                                // Cattle_Spawn_Index pre-increment with wrap (:600-603)
+          if (row >= p.n_sims) row = 0;
+          a.envi[e] = make_int4(0, 0, n, row);
+          a.envj[e] = ej;
+          a.epret[e] = 0.0;
+          s.newn[t] = n; s.row[t] = row; s.epi[t] = ej.z;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, sel);
+        if (sel) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
+        if (t == 0) s.misc[1] = __popc(m);
+      }
+      __syncthreads();
+      const int nd = s.misc[1];
+      if (nd > 0) reset_envs<T, true>(a, s, e0, nd);
+      __syncthreads();
+    }
+  }
+}
+
+// Deferred reset of the envs the step kernel listed (split mode): one WARP per finished env, no shared memory and
+// no CTA barrier, persistent grid.  Same arithmetic as reset_envs (BaseAviary.reset :280-331, _housekeeping :547-637,
+// initialize_drone_positions :251-277) -- positions at reset are analytic (line / two-row spawn, table row), so every
+// lane can rebuild what it needs; tests/test_cuda_env.py::test_split_mode_equals_fused_mode holds the two
+// implementations together bit for bit.
+template <typename T>
+__device__ __forceinline__ void spawn_xy(int d, int n, T& x, T& y) {
+  int col = d;
+  y = T(0);
+  if (n > 4) { const int n1 = n / 2; if (d >= n1) { col = d - n1; y = T(k::DRONE_SPAWN_SPACING); } }
+  x = T(col) * T(k::DRONE_SPAWN_SPACING);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
+  const KParams& p = a.p;
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int count = *a.done_count;
+  const int E = p.E, D = p.D, M = p.M, L = p.L;
+  const int RL = p.R * L;
+  const int cbase = (p.packing == CHS_PACK_MARL) ? 10 + 2 * 4 : 10 + 2 * CHS_MAX_DRONES;
+  const int nobs = (M < 16) ? M : 16;
+  for (int i = gw; i < count; i += nwarps) {
+    const int e = a.done_list[i];
+    int n = 0, row = 0, epi = 0;
+    if (lane == 0) {
+      const int4 ei = a.envi[e];
       int4 ej = a.envj[e];
-      ej.z += 1;                                         // episode index
-      const int n = draw_num_drones(p, p.env_id_offset + e, ej.z);
-      int row = ei.w + 1;                                // Cattle_Spawn_Index pre-increment with wrap (:600-603)
+      ej.z += 1; epi = ej.z;
+      n = draw_num_drones(p, p.env_id_offset + e, epi);
+      row = ei.w + 1;
       if (row >= p.n_sims) row = 0;
       a.envi[e] = make_int4(0, 0, n, row);
       a.envj[e] = ej;
       a.epret[e] = 0.0;
-      s.newn[t] = n; s.row[t] = row; s.epi[t] = ej.z;
     }
-    const unsigned m = __ballot_sync(0xffffffffu, sel);
-    if (sel) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
-    if (t == 0) s.misc[1] = __popc(m);
+    n = __shfl_sync(full, n, 0); row = __shfl_sync(full, row, 0); epi = __shfl_sync(full, epi, 0);
+    const typename VT<T>::v2* srow = a.spawn + (size_t)row * p.spawn_stride;
+    for (int j = lane; j < M; j += 32) {                       // cows (BaseAviary.py:611-637)
+      const auto xy = srow[j];
+      uint32_t c[4] = {(uint32_t)(p.env_id_offset + e), (uint32_t)epi, (uint32_t)j, (uint32_t)TAG_COW};
+      philox4x32_10(c, p.seed_lo, p.seed_hi);
+      T sn, cs;
+      Mth<T>::sincospi(T(2.0 * u01_24(c[1]) - 1.0), &sn, &cs);
+      a.cpos[(size_t)j * E + e] = xy;
+      a.cvel[(size_t)j * E + e] = mk2<T>(T(k::MAX_VEL_CATTLE) * cs, T(k::MAX_VEL_CATTLE) * sn);
+    }
+    for (int d = lane; d < D; d += 32) {                       // drones: every slot's kinematics zeroed, PID kept
+      DroneState<T> ds;
+      load_drone<T>(a, d, e, ds);
+#pragma unroll
+      for (int q = 0; q < 3; ++q) { ds.p[q] = 0; ds.v[q] = 0; ds.w[q] = 0; ds.rpy[q] = 0; ds.av[q] = 0; }
+      ds.q[0] = ds.q[1] = ds.q[2] = ds.q[3] = 0;
+      if (d < n) { spawn_xy<T>(d, n, ds.p[0], ds.p[1]); ds.p[2] = T(k::TARGET_ALT); ds.q[3] = T(1); }
+      store_drone<T>(a, d, e, ds);
+      a.rpm[(size_t)d * E + e] = mk4<T>(0, 0, 0, 0);
+    }
+    if (a.obs == nullptr) continue;
+    // two nearest other drones of drone `lane` (strict '<' keeps index order on ties, like drone_neighbors)
+    int j1 = -1, j2 = -1;
+    if (lane < n) {
+      T mx, my;
+      spawn_xy<T>(lane, n, mx, my);
+      T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
+      for (int j = 0; j < n; ++j) {
+        if (j == lane) continue;
+        T ox, oy;
+        spawn_xy<T>(j, n, ox, oy);
+        const T dx = ox - mx, dy = oy - my;
+        const T dist = Mth<T>::sqrt(dx * dx + dy * dy);
+        if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
+        else if (dist < d2) { d2 = dist; j2 = j; }
+      }
+    }
+    float* ob = a.obs + (size_t)e * RL;
+    for (int d = 0; d < n && d < p.R; ++d) {
+      T mx, my;
+      spawn_xy<T>(d, n, mx, my);
+      const int nb1 = __shfl_sync(full, j1, d), nb2 = __shfl_sync(full, j2, d);
+      for (int c = lane; c < L; c += 32) {
+        float v = 0.f;
+        if (c == 0) v = (float)T(k::TARGET_ALT);
+        else if (c >= 10 && c < 14) {
+          const int nb = (c < 12) ? nb1 : nb2;
+          if (nb >= 0) { T ox, oy; spawn_xy<T>(nb, n, ox, oy); v = (c & 1) ? (float)(oy - my) : (float)(ox - mx); }
+        } else if (c >= cbase && c < cbase + 2 * nobs) {
+          const auto xy = srow[(c - cbase) >> 1];
+          v = ((c - cbase) & 1) ? (float)(xy.y - my) : (float)(xy.x - mx);
+        }
+        ob[d * L + c] = v;
+      }
+    }
+    for (int idx = (n < p.R ? n : p.R) * L + lane; idx < RL; idx += 32) ob[idx] = 0.f;
   }
-  __syncthreads();
-  const int nd = s.misc[1];
-  if (nd > 0) reset_envs<T, true>(a, s, e0, nd);
 }
 
 // Split mode, kernel 1 of 2: one thread per (drone slot, env), env index fastest.  action -> PID -> K DYN substeps in
@@ -241,6 +366,7 @@ __global__ void __launch_bounds__(256) drone_kernel(const KArgs<T> a) {
   const KParams& p = a.p;
   const int E = p.E, D = p.D;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx == 0 && a.done_count) *a.done_count = 0;      // the list of finished envs is rebuilt by this step's step_kernel
   if (idx >= (long long)D * E) return;
   const int d = (int)(idx / E), e = (int)(idx - (long long)d * E);
   const int n = a.envi[e].z;
@@ -549,11 +675,16 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   if (t < 32) {
     bool fin = false;
     const int e = e0 + t;
-    if (t < G && e < E) {
+    const bool active = (t < G && e < E);
+    // values that cross the warp-converged statistics block below
+    int4 ej = pre_j;
+    double2 ef = pre_f;
+    const int4 ei = pre_i;
+    bool st_term = false, st_trunc = false, st_bad = false, done_env = false;
+    int st_cause = -1, sc = 0, scA = 0, nn = 0, row = 0;
+    double epret = 0;
+    if (active) {
       const int n = s.n[t];
-      const int4 ei = pre_i;
-      int4 ej = pre_j;
-      double2 ef = pre_f;
       int level = ej.x;
       const int level_in = level;
       // sums in the reference's order: drone by drone, nearest neighbour first (CattleAviary.py:231-247).
@@ -684,27 +815,70 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       ej.x = level;
       CHS_STAMP(8);
       if (a.dbg_herded) a.dbg_herded[e] = herded;
-      double epret = pre_ret + r_global;
-      int sc = ei.x + sc_inc, scA = ei.y + 1, nn = n, row = ei.w;
+      epret = pre_ret + r_global;
+      sc = ei.x + sc_inc; scA = ei.y + 1; nn = n; row = ei.w;
       fin = term || trunc;
-      if (!(r_global == r_global) || fabs(r_global) == Mth<double>::inf()) atomicAdd(a.stats + 9, 1.0);
-      if (fin) {
-        atomicAdd(a.stats + 0, 1.0);
-        atomicAdd(a.stats + 1, epret);
-        atomicAdd(a.stats + 2, (double)scA);
-        if (term) atomicAdd(a.stats + 3, 1.0);
-        if (trunc) atomicAdd(a.stats + 4 + cause, 1.0);
+      st_term = term; st_trunc = trunc; st_cause = cause;
+      st_bad = !(r_global == r_global) || fabs(r_global) == Mth<double>::inf();
+      done_env = fin && p.auto_reset;          // the observation of this step goes to term_obs, a fresh one to obs
+    }
+    // ---- warp-converged: episode statistics and list slots with ONE atomic per counter per warp.  Thousands of
+    // finished envs per step hitting the same few addresses with one atomic each serialise in L2. ----
+    {
+      const unsigned full = 0xffffffffu, lt = (1u << t) - 1u;
+      const unsigned fm = __ballot_sync(full, fin);
+      const unsigned bm = __ballot_sync(full, st_bad);
+      if (bm && t == 0) atomicAdd(a.stats + 9, (double)__popc(bm));
+      if (fm) {
+        double ret = fin ? epret : 0.0;
+        int len = fin ? scA : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { ret += __shfl_xor_sync(full, ret, o); len += __shfl_xor_sync(full, len, o); }
+        const unsigned tm = __ballot_sync(full, fin && st_term);
+        unsigned cm[5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) cm[c] = __ballot_sync(full, fin && st_trunc && st_cause == c);
+        if (t == 0) {
+          atomicAdd(a.stats + 0, (double)__popc(fm));
+          atomicAdd(a.stats + 1, ret);
+          atomicAdd(a.stats + 2, (double)len);
+          if (tm) atomicAdd(a.stats + 3, (double)__popc(tm));
+#pragma unroll
+          for (int c = 0; c < 5; ++c) if (cm[c]) atomicAdd(a.stats + 4 + c, (double)__popc(cm[c]));
+        }
       }
-      if (fin && p.auto_reset) {
+      const unsigned dm = __ballot_sync(full, done_env);
+      if (dm) {
+        const int lead = __ffs(dm) - 1, cnt = __popc(dm), off = __popc(dm & lt);
+        if (a.term_mode == 2) {
+          int base = 0;
+          if (t == lead) base = atomicAdd(a.term_count, cnt);
+          base = __shfl_sync(full, base, lead);
+          if (done_env) { a.term_idx[base + off] = e; s.termrow[t] = base + off; }
+        } else if (done_env) {
+          s.termrow[t] = 0;
+        }
+        if (done_env) s.done[t] = 1;
+        if (a.done_list) {
+          // deferred reset (split mode): finished envs are only listed; reset_list_kernel, launched right after
+          // this kernel, advances their episode counters and rebuilds them: CTAs here do not wait on the reset path
+          int base = 0;
+          if (t == lead) base = atomicAdd(a.done_count, cnt);
+          base = __shfl_sync(full, base, lead);
+          if (done_env) a.done_list[base + off] = e;
+        }
+      }
+    }
+    if (active) {
+      if (a.done_list) {
+        fin = false;
+      } else if (done_env) {
         ej.z += 1;
         nn = draw_num_drones(p, p.env_id_offset + e, ej.z);
         row = ei.w + 1;
         if (row >= p.n_sims) row = 0;
         sc = 0; scA = 0; epret = 0;
-        s.done[t] = 1; s.newn[t] = nn; s.row[t] = row; s.epi[t] = ej.z;
-        int trow = 0;
-        if (a.term_mode == 2) { trow = atomicAdd(a.term_count, 1); a.term_idx[trow] = e; }
-        s.termrow[t] = trow;
+        s.newn[t] = nn; s.row[t] = row; s.epi[t] = ej.z;
       } else {
         fin = false;
       }
@@ -716,7 +890,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         // phase 4 folded in: this thread knows where its env's observation goes and ships it with two bulk stores
         const size_t RL = (size_t)p.R * p.L;
         float* dst = a.obs ? a.obs + (size_t)e * RL : nullptr;
-        if (fin) {
+        if (done_env) {
           dst = nullptr;
           if (a.term_obs) dst = a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[t] : (size_t)e) * RL;
         }

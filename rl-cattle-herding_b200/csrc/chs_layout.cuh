@@ -70,6 +70,8 @@ template <typename T> struct KArgs {
   int* term_count;                   // mode 2: atomic row counter
   int* term_idx;                     // mode 2: env index of each compact row
   const uint8_t* reset_mask;         // reset kernel only (nullable = all)
+  int* done_list;                    // deferred reset (split mode): env ids finished this step (nullable = reset in the kernel)
+  int* done_count;                   // number of entries, zeroed by drone_kernel
   int* dbg_neighbors;                // nullable [E][D][2]
   int* dbg_herded;                   // nullable [E]
   long long* dbg_clock;              // nullable [grid][16]: clock64() of thread 0 at phase and sub-phase boundaries

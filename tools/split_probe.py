@@ -6,5 +6,5 @@ env = pkg.CattleHerdingBatchedEnv(E, num_drones=D, num_cattle=M, ctrl_freq=30, f
 env.set_launch(32, 256); pkg._lib.check(env.lib.chs_set_register_variant(env._h, 2))
 env.reset()
 acts = [torch.rand((E, D, 4), device="cuda") * 2 - 1 for _ in range(4)]
-for i in range(12): env.step(acts[i % 4])
+for i in range(int(os.environ.get("NSTEPS", 12))): env.step(acts[i % 4])
 torch.cuda.synchronize()
