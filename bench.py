@@ -298,11 +298,11 @@ def run_cuda_arm(args):
                        "sharding": "env index, no collective on the step path; one NCCL all-reduce of the stats vector after the run"},
             "drone_steps_per_s": value * N,
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / K,
-            "gpu_launches": K * (2 if tuned[3] == "split" else 1),
+            "gpu_launches": K * (3 if tuned[3] == "split" else 1),   # split: drone_kernel, step_kernel, reset_list_kernel
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": recorded_traffic(wl_key), "bytes_per_env_step": bytes_env,
                          "bytes_per_launch": bytes_env * E, "peak_source": peak_src,
-                         "kernel": "chs::step_kernel<float>" if tuned[3] == "fused" else "chs::drone_kernel<float> + chs::step_kernel<float> (one control step)",
+                         "kernel": "chs::step_kernel<float>" if tuned[3] == "fused" else "chs::drone_kernel<float> + chs::step_kernel<float> + chs::reset_list_kernel<float> (one control step)",
                          "kernel_ms": float(np.mean(per_step_ms))},
             "clocks": clocks.summary(),
             "episodes": {"finished": float(stats[0].item()), "mean_length": float(stats[2].item() / max(1.0, stats[0].item())),

@@ -403,7 +403,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   if (defer) {
     KArgs<T> r = base_args<T>(h);
     r.done_list = h->done_list; r.done_count = h->done_count; r.obs = obs;
-    reset_list_kernel<T><<<148 * 4, 256, 0, st>>>(r);
+    reset_list_kernel<T><<<148 * 8, 256, 0, st>>>(r);
   }
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;

@@ -336,22 +336,28 @@ __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
       }
     }
     float* ob = a.obs + (size_t)e * RL;
+    // lane l holds component (l & 1) of cow (l >> 1): the 32 cattle columns of every row come from one register
+    T cow_c = T(0);
+    const bool cow_ok = (lane >> 1) < nobs;
+    if (cow_ok) { const auto xy = srow[lane >> 1]; cow_c = (lane & 1) ? xy.y : xy.x; }
     for (int d = 0; d < n && d < p.R; ++d) {
       T mx, my;
       spawn_xy<T>(d, n, mx, my);
       const int nb1 = __shfl_sync(full, j1, d), nb2 = __shfl_sync(full, j2, d);
-      for (int c = lane; c < L; c += 32) {
-        float v = 0.f;
-        if (c == 0) v = (float)T(k::TARGET_ALT);
-        else if (c >= 10 && c < 14) {
-          const int nb = (c < 12) ? nb1 : nb2;
-          if (nb >= 0) { T ox, oy; spawn_xy<T>(nb, n, ox, oy); v = (c & 1) ? (float)(oy - my) : (float)(ox - mx); }
-        } else if (c >= cbase && c < cbase + 2 * nobs) {
-          const auto xy = srow[(c - cbase) >> 1];
-          v = ((c - cbase) & 1) ? (float)(xy.y - my) : (float)(xy.x - mx);
+      float* orow = ob + d * L;
+      {   // columns 0 .. cbase-1: z, zeros, two neighbour slots, zeros (cbase <= 34: two passes at most)
+        for (int c = lane; c < cbase; c += 32) {
+          float v = 0.f;
+          if (c == 0) v = (float)T(k::TARGET_ALT);
+          else if (c >= 10 && c < 14) {
+            const int nb = (c < 12) ? nb1 : nb2;
+            if (nb >= 0) { T ox, oy; spawn_xy<T>(nb, n, ox, oy); v = (c & 1) ? (float)(oy - my) : (float)(ox - mx); }
+          }
+          orow[c] = v;
         }
-        ob[d * L + c] = v;
       }
+      if (cbase + lane < L) orow[cbase + lane] = cow_ok ? (float)(cow_c - ((lane & 1) ? my : mx)) : 0.f;
+      for (int c = cbase + 32 + lane; c < L; c += 32) orow[c] = 0.f;
     }
     for (int idx = (n < p.R ? n : p.R) * L + lane; idx < RL; idx += 32) ob[idx] = 0.f;
   }
