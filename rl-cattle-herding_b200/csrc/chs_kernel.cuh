@@ -537,9 +537,16 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
           }
           s.dpos[it] = mk4<T>(A.x, A.y, A.z, T(0));
           float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
-          row[0] = (float)A.z; row[1] = (float)A.w; row[2] = (float)C.w; row[3] = (float)O.w;
-          row[4] = (float)C.x; row[5] = (float)C.y; row[6] = (float)C.z;
-          row[7] = (float)O.x; row[8] = (float)O.y; row[9] = (float)O.z;
+          if ((p.L & 1) == 0) {
+            float2* r2 = reinterpret_cast<float2*>(row);
+            r2[0] = make_float2((float)A.z, (float)A.w); r2[1] = make_float2((float)C.w, (float)O.w);
+            r2[2] = make_float2((float)C.x, (float)C.y); r2[3] = make_float2((float)C.z, (float)O.x);
+            r2[4] = make_float2((float)O.y, (float)O.z);
+          } else {
+            row[0] = (float)A.z; row[1] = (float)A.w; row[2] = (float)C.w; row[3] = (float)O.w;
+            row[4] = (float)C.x; row[5] = (float)C.y; row[6] = (float)C.z;
+            row[7] = (float)O.x; row[8] = (float)O.y; row[9] = (float)O.z;
+          }
         }
       }
     }
