@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--cattle", type=int, default=20)
     ap.add_argument("--ctrl-freq", type=int, default=30)
     ap.add_argument("--launch", default="auto", help="'auto' or G,threads")
+    ap.add_argument("--packing", default="ctde", choices=["ctde", "marl"],
+                    help="ctde: sb3_envs CattleAviary (the BASELINE workload); marl: rllib_envs MARLCattleAviary semantics")
     ap.add_argument("--step-mode", default="auto", choices=["auto", "fused", "split"],
                     help="fused: one kernel per control step; split: drone_kernel + step_kernel; auto: the faster one (untimed probe)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -236,7 +238,7 @@ def run_cuda_arm(args):
     table = pkg.spawn.generate(100 if M <= 32 else 8, M, seed=0)
     env = pkg.CattleHerdingBatchedEnv(E, num_drones=N, num_cattle=M, ctrl_freq=args.ctrl_freq, fixed_num_drones=N,
                                       start_level=7, auto_reset=True, spawn_table=table, device=dev.index,
-                                      env_id_offset=rank * E, seed=0)
+                                      env_id_offset=rank * E, seed=0, packing=args.packing)
     gen = torch.Generator(device=dev).manual_seed(1 + rank)
     action_pool = [torch.rand((E, N, 4), device=dev, generator=gen) * 2 - 1 for _ in range(16)]
     flush_buf = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
@@ -289,7 +291,8 @@ def run_cuda_arm(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"CattleAviary Physics.DYN, {N} drones + {M} cattle, {E} envs per GPU, VEL actions, "
-                                   f"240 Hz physics / {args.ctrl_freq} Hz ctrl, level 7, uniform random actions, auto-reset",
+                                   f"240 Hz physics / {args.ctrl_freq} Hz ctrl, level 7, uniform random actions, auto-reset"
+                                   + (", MARL packing" if args.packing == "marl" else ""),
                        "envs_per_gpu": E, "total_envs": world * E, "obs_shape": [dims["obs_rows"], dims["obs_len"]],
                        "launch": {"envs_per_block": tuned[1], "threads_per_block": tuned[2], "smem_bytes": env.dims["smem_bytes"],
                                   "step_mode": tuned[3]},
@@ -328,10 +331,14 @@ def run_cuda_arm(args):
         if dist is not None:
             dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
         if rank == 0:
-            RL = dims["obs_rows"] * dims["obs_len"]
+            # only the first max_drones rows of an observation image are copied (the rest is constant zero padding)
+            RLc = min(dims["obs_rows"], dims["max_drones"]) * dims["obs_len"]
+            # one block with count | reward | flags | done indices, plus E/8 speculative terminal observations per step
+            small = 16 + E * 4 + 2 * ((E + 15) // 16 * 16) + E * 4
+            spec = max(E // 8, 64) if E >= 64 else E
             line["e2e"] = {"value": world * E * Ke / float(e2e_s.item()), "unit": "env-steps/s",
                            "h2d_bytes_per_step": E * N * 4 * 4,
-                           "d2h_bytes_per_step": E * (RL * 4 + 4 + 2) + 4 + int(nterm / Ke * (RL * 4 + 4)),
+                           "d2h_bytes_per_step": E * RLc * 4 + small + int(max(spec, nterm / Ke) * RLc * 4),
                            "steps": Ke, "api": "CattleHerdingBatchedEnv.step_host (chs_step_host): pinned numpy in/out"}
 
     # ---- larger batches on the same GPU (inputs > L2, no flush needed), rank 0 of N=1 only ----

@@ -162,7 +162,10 @@ int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, float* rewa
  * the handle's pinned staging area, results D2H, and the call returns after the stream has
  * drained.  Terminal observations come back compacted: *n_done_host envs finished, their indices
  * are in done_idx_host[0..n) (capacity E) and their terminal observations in
- * terminal_obs_host[i][R][L] (capacity E rows); both may be NULL. */
+ * terminal_obs_host[i][R][L] (capacity E rows); both may be NULL.
+ * Observation rows >= max_drones are identically zero, so only the first max_drones rows of every image cross
+ * PCIe; the padding rows of obs_host / terminal_obs_host are zero-filled by the library the first time it sees a
+ * buffer (by address) and are not rewritten afterwards -- do not scribble on them. */
 int chs_step_host(ChsHandle* h, const float* actions_host, float* obs_host, float* reward_host,
                   uint8_t* terminated_host, uint8_t* truncated_host, int32_t* n_done_host,
                   int32_t* done_idx_host, float* terminal_obs_host, void* stream);

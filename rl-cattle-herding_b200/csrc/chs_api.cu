@@ -47,6 +47,15 @@ struct ChsHandle {
   int* done_list;
   int* done_count;
   int step_mode;      // 0 auto, 1 fused (one kernel), 2 split (drone_kernel + step_kernel)
+  // experiment knobs, read from the environment once at creation (tools/residency_probe.py and A/B runs):
+  // CHS_SMEM_PAD=<bytes> extra dynamic shared memory per CTA, CHS_NO_BULK=1 warp copy-out instead of bulk stores,
+  // CHS_FULL_KERNEL=1 never use the lean build, CHS_INLINE_RESET=1 reset inside step_kernel in split mode too
+  unsigned char* d_small;           // host path: count | reward | flags | done idx in one block (chs_api_io.inc)
+  unsigned char* h_small;           // pinned mirror
+  const void* zeroed_obs_host;      // host buffers whose padding rows have been zero-filled (chs_api_io.inc)
+  const void* zeroed_termobs_host;
+  int knob_smem_pad;
+  bool knob_full, knob_inline_reset;
   int *dbg_nb, *dbg_herd;
   long long* dbg_clock;
   int threads, smem;
@@ -91,8 +100,7 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
   if (G < 1 || G > 32 || (G & (G - 1))) return fail(CHS_ERR_INVALID, "envs_per_block must be a power of two in 1..32");
   if (threads < 32 || threads > 512 || (threads & 31)) return fail(CHS_ERR_INVALID, "threads_per_block must be a multiple of 32 in 32..512");
   int smem = smem_for(h, G);
-  // experiment knob: unused extra shared memory per CTA to lower the number of resident CTAs per SM
-  if (const char* pad = getenv("CHS_SMEM_PAD")) smem += atoi(pad);
+  smem += h->knob_smem_pad;
   // the opt-in limit is a per-function, process-wide attribute: always raise it to the cap so that handles with
   // different shared-memory needs can coexist (the launch's own size decides occupancy)
   if (smem > kSmemCap) return fail(CHS_ERR_INVALID, "shared memory need %d B exceeds the per-CTA budget", smem);
@@ -186,6 +194,9 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
     kp.zero_bytes = kp.bulk_ok ? total - c1 : 0;
   }
   h->step_mode = prm->reserved0;
+  { const char* v = getenv("CHS_SMEM_PAD"); h->knob_smem_pad = v ? atoi(v) : 0; }
+  h->knob_full = getenv("CHS_FULL_KERNEL") != nullptr;
+  h->knob_inline_reset = getenv("CHS_INLINE_RESET") != nullptr;
   kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
   kp.aero_flags = prm->aero_flags;
@@ -252,9 +263,9 @@ extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
   void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count,
-                  h->d_actions, h->d_obs, h->d_reward, h->d_termobs, h->d_term, h->d_trunc, h->d_mask, h->d_count, h->d_idx};
+                  h->d_actions, h->d_obs, h->d_small, h->d_termobs, h->d_mask};
   for (void* p : ptrs) if (p) cudaFree(p);
-  if (h->h_count) cudaFreeHost(h->h_count);
+  if (h->h_small) cudaFreeHost(h->h_small);
   free(h);
   return CHS_OK;
 }
@@ -375,7 +386,7 @@ template <> void launch_step_variant<float>(ChsHandle* h, const KArgs<float>& a,
   const bool big = (h->reg_variant == 2 && h->threads <= 256) || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
   const bool marl = h->kp.packing == CHS_PACK_MARL, split = a.p.split != 0;
   // lean build unless a runtime-checked feature is in use
-  const bool full = a.p.aero_flags || a.p.cattle_integrate || !a.p.cp_ok || !a.p.bulk_ok || a.dbg_clock || getenv("CHS_FULL_KERNEL");
+  const bool full = a.p.aero_flags || a.p.cattle_integrate || !a.p.cp_ok || !a.p.bulk_ok || a.dbg_clock || h->knob_full;
   if (full) { if (big) CHS_LAUNCH(float, 256, 4, true); else CHS_LAUNCH(float, 512, 1, true); }
   else      { if (big) CHS_LAUNCH(float, 256, 4, false); else CHS_LAUNCH(float, 512, 1, false); }
 }
@@ -393,11 +404,11 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   if (split) {
     if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
     const long long nthr = (long long)h->kp.D * h->E;
-    if (h->kp.auto_reset && !getenv("CHS_INLINE_RESET")) a.done_count = h->done_count;
+    if (h->kp.auto_reset && !h->knob_inline_reset) a.done_count = h->done_count;
     drone_kernel<T><<<(unsigned)((nthr + 255) / 256), 256, 0, st>>>(a);
     a.p.split = 1;
   }
-  const bool defer = split && h->kp.auto_reset && !getenv("CHS_INLINE_RESET");
+  const bool defer = split && h->kp.auto_reset && !h->knob_inline_reset;
   if (defer) { a.done_list = h->done_list; a.done_count = h->done_count; }
   launch_step_variant<T>(h, a, grid, st);
   if (defer) {
