@@ -193,7 +193,7 @@ int chs_set_register_variant(ChsHandle* h, int32_t variant);
 int chs_set_step_mode(ChsHandle* h, int32_t mode);
 
 /* Profiling aid: when non-NULL, thread 0 of every CTA of chs_step writes clock64() at the 7 phase boundaries
- * of the fused kernel into int64 [grid][16] (13 stamps used) (grid = ceil(E / envs_per_block)).  NULL disables. */
+ * of the fused kernel into int64 [grid][32] (24 stamps used) (grid = ceil(E / envs_per_block)).  NULL disables. */
 int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev);
 
 /* Episode statistics accumulated on device since the last reset of the accumulator:

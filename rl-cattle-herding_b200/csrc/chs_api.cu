@@ -243,6 +243,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
     std::vector<double> tab(152, 0.0);
     for (int l = 0; l < k::NUM_LEVELS; ++l) for (int c = 0; c < k::C_NCOLS; ++c) tab[l * k::C_NCOLS + c] = h_curr[l][c];
     for (int n = 1; n <= CHS_MAX_DRONES; ++n) tab[CHS_TAB_INV_N + n] = 1.0 / n;
+    tab[CHS_TAB_APPROACH] = 5.0 / (k::SPEED_LIMIT / (double)h->kp.ctrl_freq + 1e-6);
+    tab[CHS_TAB_INV_M] = h->kp.M > 0 ? 1.0 / (double)h->kp.M : 0.0;
     err = cudaMemcpy(h->tab, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice);
     if (err != cudaSuccess) { chs_destroy(h); return fail(CHS_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(err)); }
   }

@@ -47,7 +47,7 @@ __device__ __forceinline__ void store_drone(const KArgs<T>& a, int d, int e, con
 // The scipy Euler round trip of the target rotation (:205,242-244) is the identity on the rotation
 // (oracle/cattle_oracle.py:_pid), so the target frame is carried as its three columns.
 template <typename T>
-__device__ __forceinline__ void dsl_pid(DroneState<T>& s, const T tp[3], T target_yaw, const T tv[3],
+__device__ __forceinline__ void dsl_pid(DroneState<T>& s, const T tp[3], T target_yaw, bool yaw_is_state, const T tv[3],
                                         T ctrl_dt, T ctrl_freq, T rpm[4]) {
   T R[3][3];
   quat_to_matrix<T>(s.q, R);
@@ -70,7 +70,18 @@ __device__ __forceinline__ void dsl_pid(DroneState<T>& s, const T tp[3], T targe
   const T inF = Mth<T>::rsqrt(F[0] * F[0] + F[1] * F[1] + F[2] * F[2]);
   const T zb[3] = {F[0] * inF, F[1] * inF, F[2] * inF};
   T sy, cy;
-  Mth<T>::sincos(target_yaw, &sy, &cy);
+  if (!yaw_is_state) {
+    sy = T(0); cy = T(1);          // every other PID-driven action type asks for yaw 0
+  } else if (sizeof(T) == 4) {
+    // VEL: the target yaw is the state's own yaw = atan2(R10, R00) of the stored quaternion (pybullet ZYX), so its
+    // sine / cosine are R10, R00 over cos(pitch) -- no trigonometric range reduction on the drone's serial chain.
+    // Inside the gimbal guard of getEulerFromQuaternion (cos^2(pitch) <= 2e-5) the stored yaw is used as is.
+    const T h2 = R[0][0] * R[0][0] + R[1][0] * R[1][0];
+    if (h2 > T(2.1e-5)) { const T ih = Mth<T>::rsqrt(h2); cy = R[0][0] * ih; sy = R[1][0] * ih; }
+    else Mth<T>::sincos(target_yaw, &sy, &cy);
+  } else {
+    Mth<T>::sincos(target_yaw, &sy, &cy);
+  }
   // zb x (cy, sy, 0)
   const T c0 = -zb[2] * sy, c1 = zb[2] * cy, c2 = zb[0] * sy - zb[1] * cy;
   const T inc = Mth<T>::rsqrt(c0 * c0 + c1 * c1 + c2 * c2);
@@ -145,7 +156,7 @@ __device__ __forceinline__ void action_to_rpm(const KParams& p, DroneState<T>& s
       for (int i = 0; i < 3; ++i) tp[i] = s.p[i] + d[i] / dist;   // rare branch, exact
     }
   }
-  if (pid) dsl_pid<T>(s, tp, tyaw, tv, ctrl_dt, cf, rpm);
+  if (pid) dsl_pid<T>(s, tp, tyaw, p.act == 0, tv, ctrl_dt, cf, rpm);
 }
 
 // K substeps of BaseAviary._dynamics (:1043-1102) + _integrateQ (:1104-1117) with constant rpm.

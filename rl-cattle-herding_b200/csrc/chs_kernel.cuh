@@ -72,6 +72,7 @@ __device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, unsigne
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // One env's observation image = staged rows followed by zero padding (from the CTA's zero block) up to R*L floats.
@@ -272,6 +273,92 @@ __device__ __forceinline__ void spawn_xy(int d, int n, T& x, T& y) {
   x = T(col) * T(k::DRONE_SPAWN_SPACING);
 }
 
+// One finished env rebuilt by one warp (all 32 lanes call; n / row / epi are warp-uniform): cows from the spawn row
+// with Philox velocity angles, drone slots zeroed except the PID state, and the first observation of the new episode
+// written straight from registers -- everything a fresh episode shows is analytic in (n, row).
+// `parts` selects what this call does (bit 0 cows, bit 1 drones, bit 2 observation): the three are independent, so the
+// fused kernel hands them to different warps.
+enum ResetPart { RESET_COWS = 1, RESET_DRONES = 2, RESET_OBS = 4, RESET_ALL = 7 };
+template <typename T>
+__device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, int row, int epi, int lane, int parts) {
+  const KParams& p = a.p;
+  const unsigned full = 0xffffffffu;
+  const int E = p.E, D = p.D, M = p.M, L = p.L;
+  const int RL = p.R * L;
+  const int cbase = (p.packing == CHS_PACK_MARL) ? 10 + 2 * 4 : 10 + 2 * CHS_MAX_DRONES;
+  const int nobs = (M < 16) ? M : 16;
+  const typename VT<T>::v2* srow = a.spawn + (size_t)row * p.spawn_stride;
+  if (parts & RESET_COWS) for (int j = lane; j < M; j += 32) {                       // cows (BaseAviary.py:611-637)
+    const auto xy = srow[j];
+    uint32_t c[4] = {(uint32_t)(p.env_id_offset + e), (uint32_t)epi, (uint32_t)j, (uint32_t)TAG_COW};
+    philox4x32_10(c, p.seed_lo, p.seed_hi);
+    T sn, cs;
+    Mth<T>::sincospi(T(2.0 * u01_24(c[1]) - 1.0), &sn, &cs);
+    a.cpos[(size_t)j * E + e] = xy;
+    a.cvel[(size_t)j * E + e] = mk2<T>(T(k::MAX_VEL_CATTLE) * cs, T(k::MAX_VEL_CATTLE) * sn);
+  }
+  if (parts & RESET_DRONES) for (int d = lane; d < D; d += 32) {   // drones: every slot's kinematics zeroed, PID kept
+    DroneState<T> ds;
+    load_drone<T>(a, d, e, ds);
+#pragma unroll
+    for (int q = 0; q < 3; ++q) { ds.p[q] = 0; ds.v[q] = 0; ds.w[q] = 0; ds.rpy[q] = 0; ds.av[q] = 0; }
+    ds.q[0] = ds.q[1] = ds.q[2] = ds.q[3] = 0;
+    if (d < n) { spawn_xy<T>(d, n, ds.p[0], ds.p[1]); ds.p[2] = T(k::TARGET_ALT); ds.q[3] = T(1); }
+    store_drone<T>(a, d, e, ds);
+    a.rpm[(size_t)d * E + e] = mk4<T>(0, 0, 0, 0);
+  }
+  if (a.obs == nullptr || !(parts & RESET_OBS)) return;
+  // two nearest other drones of drone `lane` (strict '<' keeps index order on ties, like drone_neighbors)
+  int j1 = -1, j2 = -1;
+  if (lane < n) {
+    T mx, my;
+    spawn_xy<T>(lane, n, mx, my);
+    T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
+    for (int j = 0; j < n; ++j) {
+      if (j == lane) continue;
+      T ox, oy;
+      spawn_xy<T>(j, n, ox, oy);
+      const T dx = ox - mx, dy = oy - my;
+      const T dist = Mth<T>::sqrt(dx * dx + dy * dy);
+      if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
+      else if (dist < d2) { d2 = dist; j2 = j; }
+    }
+  }
+  float* ob = a.obs + (size_t)e * RL;
+  // lane l holds component (l & 1) of cow (l >> 1): the 32 cattle columns of every row come from one register
+  T cow_c = T(0);
+  const bool cow_ok = (lane >> 1) < nobs;
+  if (cow_ok) { const auto xy = srow[lane >> 1]; cow_c = (lane & 1) ? xy.y : xy.x; }
+  for (int d = 0; d < n && d < p.R; ++d) {
+    T mx, my;
+    spawn_xy<T>(d, n, mx, my);
+    const int nb1 = __shfl_sync(full, j1, d), nb2 = __shfl_sync(full, j2, d);
+    float* orow = ob + d * L;
+    {   // columns 0 .. cbase-1: z, zeros, two neighbour slots, zeros (cbase <= 34: two passes at most)
+      for (int c = lane; c < cbase; c += 32) {
+        float v = 0.f;
+        if (c == 0) v = (float)T(k::TARGET_ALT);
+        else if (c >= 10 && c < 14) {
+          const int nb = (c < 12) ? nb1 : nb2;
+          if (nb >= 0) { T ox, oy; spawn_xy<T>(nb, n, ox, oy); v = (c & 1) ? (float)(oy - my) : (float)(ox - mx); }
+        }
+        orow[c] = v;
+      }
+    }
+    if (cbase + lane < L) orow[cbase + lane] = cow_ok ? (float)(cow_c - ((lane & 1) ? my : mx)) : 0.f;
+    for (int c = cbase + 32 + lane; c < L; c += 32) orow[c] = 0.f;
+  }
+  const int zfrom = (n < p.R ? n : p.R) * L;
+  if (p.vec4_ok) {       // R*L is a multiple of 4 and the image is 16-byte aligned: the zero rows go out as float4
+    const int z4 = (zfrom + 3) >> 2;
+    if (zfrom + lane < (z4 << 2)) ob[zfrom + lane] = 0.f;        // up to 3 floats to the next 16-byte boundary
+    float4* o4 = reinterpret_cast<float4*>(ob);
+    for (int r = z4 + lane; r < (RL >> 2); r += 32) o4[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+  } else {
+    for (int idx = zfrom + lane; idx < RL; idx += 32) ob[idx] = 0.f;
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
   const KParams& p = a.p;
@@ -279,10 +366,6 @@ __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
   const int lane = threadIdx.x & 31;
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
   const int count = *a.done_count;
-  const int E = p.E, D = p.D, M = p.M, L = p.L;
-  const int RL = p.R * L;
-  const int cbase = (p.packing == CHS_PACK_MARL) ? 10 + 2 * 4 : 10 + 2 * CHS_MAX_DRONES;
-  const int nobs = (M < 16) ? M : 16;
   for (int i = gw; i < count; i += nwarps) {
     const int e = a.done_list[i];
     int n = 0, row = 0, epi = 0;
@@ -298,68 +381,7 @@ __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
       a.epret[e] = 0.0;
     }
     n = __shfl_sync(full, n, 0); row = __shfl_sync(full, row, 0); epi = __shfl_sync(full, epi, 0);
-    const typename VT<T>::v2* srow = a.spawn + (size_t)row * p.spawn_stride;
-    for (int j = lane; j < M; j += 32) {                       // cows (BaseAviary.py:611-637)
-      const auto xy = srow[j];
-      uint32_t c[4] = {(uint32_t)(p.env_id_offset + e), (uint32_t)epi, (uint32_t)j, (uint32_t)TAG_COW};
-      philox4x32_10(c, p.seed_lo, p.seed_hi);
-      T sn, cs;
-      Mth<T>::sincospi(T(2.0 * u01_24(c[1]) - 1.0), &sn, &cs);
-      a.cpos[(size_t)j * E + e] = xy;
-      a.cvel[(size_t)j * E + e] = mk2<T>(T(k::MAX_VEL_CATTLE) * cs, T(k::MAX_VEL_CATTLE) * sn);
-    }
-    for (int d = lane; d < D; d += 32) {                       // drones: every slot's kinematics zeroed, PID kept
-      DroneState<T> ds;
-      load_drone<T>(a, d, e, ds);
-#pragma unroll
-      for (int q = 0; q < 3; ++q) { ds.p[q] = 0; ds.v[q] = 0; ds.w[q] = 0; ds.rpy[q] = 0; ds.av[q] = 0; }
-      ds.q[0] = ds.q[1] = ds.q[2] = ds.q[3] = 0;
-      if (d < n) { spawn_xy<T>(d, n, ds.p[0], ds.p[1]); ds.p[2] = T(k::TARGET_ALT); ds.q[3] = T(1); }
-      store_drone<T>(a, d, e, ds);
-      a.rpm[(size_t)d * E + e] = mk4<T>(0, 0, 0, 0);
-    }
-    if (a.obs == nullptr) continue;
-    // two nearest other drones of drone `lane` (strict '<' keeps index order on ties, like drone_neighbors)
-    int j1 = -1, j2 = -1;
-    if (lane < n) {
-      T mx, my;
-      spawn_xy<T>(lane, n, mx, my);
-      T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
-      for (int j = 0; j < n; ++j) {
-        if (j == lane) continue;
-        T ox, oy;
-        spawn_xy<T>(j, n, ox, oy);
-        const T dx = ox - mx, dy = oy - my;
-        const T dist = Mth<T>::sqrt(dx * dx + dy * dy);
-        if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
-        else if (dist < d2) { d2 = dist; j2 = j; }
-      }
-    }
-    float* ob = a.obs + (size_t)e * RL;
-    // lane l holds component (l & 1) of cow (l >> 1): the 32 cattle columns of every row come from one register
-    T cow_c = T(0);
-    const bool cow_ok = (lane >> 1) < nobs;
-    if (cow_ok) { const auto xy = srow[lane >> 1]; cow_c = (lane & 1) ? xy.y : xy.x; }
-    for (int d = 0; d < n && d < p.R; ++d) {
-      T mx, my;
-      spawn_xy<T>(d, n, mx, my);
-      const int nb1 = __shfl_sync(full, j1, d), nb2 = __shfl_sync(full, j2, d);
-      float* orow = ob + d * L;
-      {   // columns 0 .. cbase-1: z, zeros, two neighbour slots, zeros (cbase <= 34: two passes at most)
-        for (int c = lane; c < cbase; c += 32) {
-          float v = 0.f;
-          if (c == 0) v = (float)T(k::TARGET_ALT);
-          else if (c >= 10 && c < 14) {
-            const int nb = (c < 12) ? nb1 : nb2;
-            if (nb >= 0) { T ox, oy; spawn_xy<T>(nb, n, ox, oy); v = (c & 1) ? (float)(oy - my) : (float)(ox - mx); }
-          }
-          orow[c] = v;
-        }
-      }
-      if (cbase + lane < L) orow[cbase + lane] = cow_ok ? (float)(cow_c - ((lane & 1) ? my : mx)) : 0.f;
-      for (int c = cbase + 32 + lane; c < L; c += 32) orow[c] = 0.f;
-    }
-    for (int idx = (n < p.R ? n : p.R) * L + lane; idx < RL; idx += 32) ob[idx] = 0.f;
+    reset_env_warp<T>(a, e, n, row, epi, lane, RESET_ALL);
   }
 }
 
@@ -429,8 +451,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   int ndt = (DG + 31) & ~31;          // "drone" threads: the first warps of the CTA
   if (ndt > nt) ndt = nt;
 
-#define CHS_STAMP(i) do { if (FULL && a.dbg_clock && t == 0) a.dbg_clock[(size_t)blockIdx.x * 16 + (i)] = clock64(); } while (0)
+#define CHS_STAMP(i) do { if (FULL && a.dbg_clock && t == 0) a.dbg_clock[(size_t)blockIdx.x * 32 + (i)] = clock64(); } while (0)
+#define CHS_GSTAMP(i) do { if (FULL && a.dbg_clock && t == 0) { unsigned long long gt_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_)); a.dbg_clock[(size_t)blockIdx.x * 32 + (i)] = (long long)gt_; } } while (0)
   CHS_STAMP(0);
+  CHS_GSTAMP(30);
   // ---------------- phase 0 ----------------
   // Every global read the step needs is issued here, before the first barrier, so that the DRAM round trips
   // of the herd, the env scalars and the first drone item of each drone thread overlap.
@@ -521,6 +545,21 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   CHS_STAMP(1);
   __syncthreads();
   CHS_STAMP(2);
+  // Observation traffic is 3/4 constant zeros (rows >= D of the (R, L) image).  They leave NOW, from the CTA's zero
+  // block, issued by the last warp: the write drains while the SMs compute instead of queueing behind the live rows at
+  // the end of the kernel, where every CTA of a one-wave launch would hit the memory system at the same moment.  A
+  // finished env's image goes to term_obs instead (phase 3 sends both pieces there) and its obs slot receives the
+  // first observation of the next episode, whose rows >= D are zeros as well.
+  const int ow = t - (nt - 32);             // lane index inside the last warp, < 0 elsewhere
+  const bool obs_lane = (!FULL || p.bulk_ok) && a.obs != nullptr && ow >= 0 && ow < G && e0 + ow < E;
+  if (obs_lane) {
+    const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_stride * 4u;
+    if (total > c1) {
+      fence_async_smem();
+      bulk_store(reinterpret_cast<char*>(a.obs + (size_t)(e0 + ow) * p.R * p.L) + c1, s.zeros, total - c1);
+      bulk_commit();
+    }
+  }
 
   // ---------------- phase 1 ----------------
   const int nact = s.misc[0];
@@ -568,6 +607,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         }
         T rpm[4];
         action_to_rpm<T>(p, ds, act, ctrl_dt, rpm);
+        CHS_STAMP(16);
         if (FULL && p.aero_flags) {
           const auto pr = a.rpm[(size_t)d * E + e];
           const T prev[4] = {pr.x, pr.y, pr.z, pr.w};
@@ -578,6 +618,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         } else {
           dyn_substeps<T>(ds, rpm, p.K, pyb_dt);
         }
+        CHS_STAMP(17);
         store_drone<T>(a, d, e, ds);
         a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
         s.dpos[it] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], T(0));
@@ -656,6 +697,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
                            a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr);
     }
   }
+  CHS_STAMP(19);
   {
     const int half = (nt >> 1) & ~31;
     const int tb = (t >= half) ? t - half : t + nt - half;
@@ -664,15 +706,22 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       if (e < E && d < s.n[g]) drone_cattle<T>(p, g, d, true, s.dpos, s.cpos, s.redB, s.stage);
     }
   }
+  CHS_STAMP(20);
+  // The drone warps are the critical path of the CTA (they come out of the neighbour ranking while the others have
+  // been idle since the alpha term), so the per-cow work below goes to the other warps when the CTA has any.
+  const int pw0 = (ndt < nt) ? ndt : 0;
+  const int pnw = nt - pw0;
+  const int pw = t - pw0;               // < 0 on the drone warps when they are exempt
   if (!FULL || !p.cattle_integrate) {
-    for (int it = t; it < nact * M; it += nt) {
+    if (pw >= 0) for (int it = pw; it < nact * M; it += pnw) {
       const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
       const auto ua = s.u[i * G + g];
       const auto v = herd_finish<T>(s.dpos, s.n[g], g, G, s.cpos[i * G + g], s.cvel[i * G + g], ua.x, ua.y);
       a.cvel[(size_t)i * E + e] = v;       // positions are not advanced on the DYN path
     }
   }
-  for (int it = t; it < M * G; it += nt) {
+  CHS_STAMP(21);
+  if (pw >= 0) for (int it = pw; it < M * G; it += pnw) {
     const int g = it & (G - 1);
     const int n = s.n[g];
     if (n > 0) {
@@ -683,6 +732,15 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   CHS_STAMP(5);
   __syncthreads();
   CHS_STAMP(6);
+  // The live rows leave as soon as they are complete, issued by the last warp while warp 0 works through phase 3.
+  // In-kernel auto-reset rewrites the obs slot of a finished env with ordinary stores after the next barrier, so
+  // there the issuing lane waits until its bulk write has landed (the wait overlaps phase 3 as well).
+  if (obs_lane) {
+    const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_stride * 4u;
+    fence_async_smem();
+    bulk_store(a.obs + (size_t)(e0 + ow) * p.R * p.L, s.stage + (size_t)ow * p.stage_stride, c1 < total ? c1 : total);
+    bulk_commit();
+  }
 
   // ---------------- phase 3 ----------------
   if (t < 32) {
@@ -727,7 +785,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       const double cent = sqrt(ddx * ddx + ddy * ddy + 0.0);
       CHS_STAMP(7);
       const int herded = s.herd[t];
-      const double eff = (M > 0) ? (double)herded / (double)M * 100.0 : 0.0;
+      // effectiveness in percent with the reference's own arithmetic (evaluation.py:136) where a success test compares
+      // it with a threshold (levels 4-6; a level-3 env can move up inside this step); the reward uses the fraction
+      const double eff = (M > 0 && level_in >= 3 && level_in <= 6) ? (double)herded / (double)M * 100.0 : 0.0;
+      const double eff_frac = (double)herded * s.ctab[CHS_TAB_INV_M];
       const double msd = (double)ms;
       double r_global = 0;
       bool term = false, trunc = false;
@@ -736,13 +797,13 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         double approach = 0;
         if (ef.x == ef.x) {   // prev_cent_dists is not None
           const double change = ef.x - cent;
-          approach = clipv<double>((change / (k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * 5.0, -1.0, 1.0);
+          approach = clipv<double>(change * s.ctab[CHS_TAB_APPROACH], -1.0, 1.0);
         }
         ef.x = cent;
         csum *= T(0.5) * inv_nT; ssum *= T(0.5) * inv_nT; c2d *= inv_nT;
         r_global = (double)ssum * s.ctab[level * k::C_NCOLS + k::C_W_SIMPLE] + (double)csum * s.ctab[level * k::C_NCOLS + k::C_W_COMPLEX] +
                    0.1 * s.ctab[level * k::C_NCOLS + k::C_W_SURV] + approach * s.ctab[level * k::C_NCOLS + k::C_W_APPROACH] +
-                   (eff / 100.0) * s.ctab[level * k::C_NCOLS + k::C_W_EFF] + (double)c2d * s.ctab[level * k::C_NCOLS + k::C_W_C2D];
+                   eff_frac * s.ctab[level * k::C_NCOLS + k::C_W_EFF] + (double)c2d * s.ctab[level * k::C_NCOLS + k::C_W_C2D];
         // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
         const bool term1 = compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, 1.0 / 240.0);
         if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
@@ -789,10 +850,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
           double r = (double)((s1 + s2) * T(0.5)) * s.ctab[level * k::C_NCOLS + k::C_W_SIMPLE] +
                      (double)((c1 + c2) * T(0.5)) * s.ctab[level * k::C_NCOLS + k::C_W_COMPLEX] + 0.1 * s.ctab[level * k::C_NCOLS + k::C_W_SURV];
           double approach = 0;
-          if (ef.x == ef.x) approach = clipv<double>(((ef.x - cent) / (k::SPEED_LIMIT / p.ctrl_freq + 1e-6)) * 5.0, -1.0, 1.0);
+          if (ef.x == ef.x) approach = clipv<double>((ef.x - cent) * s.ctab[CHS_TAB_APPROACH], -1.0, 1.0);
           ef.x = cent;
           r += approach * s.ctab[level * k::C_NCOLS + k::C_W_APPROACH];
-          r += (eff / 100.0) * s.ctab[level * k::C_NCOLS + k::C_W_EFF];
+          r += eff_frac * s.ctab[level * k::C_NCOLS + k::C_W_EFF];
           r += (double)B.x * s.ctab[level * k::C_NCOLS + k::C_W_C2D];
           const bool own_trunc = (B.z != T(0)) || ((double)B.y < k::COLLISION_THRESHOLD) ||
                                  (B.y > T(k::MAX_FORMATION_DISTANCE)) || shared_trunc;
@@ -882,6 +943,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         }
       }
     }
+    CHS_STAMP(22);
     if (active) {
       if (a.done_list) {
         fin = false;
@@ -899,19 +961,14 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       a.envj[e] = ej;
       a.envf[e] = ef;
       a.epret[e] = epret;
-      if (!FULL || p.bulk_ok) {
-        // phase 4 folded in: this thread knows where its env's observation goes and ships it with two bulk stores
+      CHS_STAMP(23);
+      if ((!FULL || p.bulk_ok) && done_env && a.term_obs) {
+        // terminal observation of a finished env: the whole image (staged rows + zero padding) to its term_obs row
         const size_t RL = (size_t)p.R * p.L;
-        float* dst = a.obs ? a.obs + (size_t)e * RL : nullptr;
-        if (done_env) {
-          dst = nullptr;
-          if (a.term_obs) dst = a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[t] : (size_t)e) * RL;
-        }
-        if (dst) {
-          fence_async_smem();
-          bulk_copy_rows(p, s.stage + (size_t)t * p.stage_stride, s.zeros, dst);
-          bulk_commit();
-        }
+        fence_async_smem();
+        bulk_copy_rows(p, s.stage + (size_t)t * p.stage_stride, s.zeros,
+                       a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[t] : (size_t)e) * RL);
+        bulk_commit();
       }
     }
     const unsigned m = __ballot_sync(0xffffffffu, fin);
@@ -941,11 +998,21 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   CHS_STAMP(11);
   // ---------------- phase 5 ----------------
   if (nd > 0) {
-    if (!FULL || p.bulk_ok) bulk_wait_read();     // the staging area of finished envs is rebuilt below
-    reset_envs<T, FULL>(a, s, e0, nd);
+    // (finished env, part) items over the warps, straight to global memory: no shared-memory staging.  The obs slot of a
+    // finished env already received this step's live rows through a bulk store of the last warp; that write has to
+    // land before the ordinary stores of the new episode's first observation (CTAs without a finished env skip this).
+    if (obs_lane) bulk_wait_all();
+    __syncthreads();
+    const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
+    for (int i = warp; i < 3 * nd; i += nwarp) {
+      const int g = s.dlist[i / 3];
+      reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, 1 << (i % 3));
+    }
   }
   if (!FULL || p.bulk_ok) bulk_wait_read();       // shared memory must outlive the pending bulk reads
   CHS_STAMP(12);
+  CHS_GSTAMP(31);
+#undef CHS_GSTAMP
 #undef CHS_STAMP
 }
 

@@ -74,7 +74,7 @@ template <typename T> struct KArgs {
   int* done_count;                   // number of entries, zeroed by drone_kernel
   int* dbg_neighbors;                // nullable [E][D][2]
   int* dbg_herded;                   // nullable [E]
-  long long* dbg_clock;              // nullable [grid][16]: clock64() of thread 0 at phase and sub-phase boundaries
+  long long* dbg_clock;              // nullable [grid][32]: clock64() of thread 0 at phase and sub-phase boundaries
 };
 
 // ---- shared-memory carve-up (per CTA of G envs) ----------------------------------------------------

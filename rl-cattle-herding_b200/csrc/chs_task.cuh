@@ -10,7 +10,9 @@ namespace chs {
 // phase 0, together with its other loads.  A __constant__ table indexed by the per-env level costs a constant-
 // cache miss (a DRAM round trip when L2 is cold) on the serial per-env path; the shared copy costs one LDS.
 constexpr int CHS_TAB_INV_N = k::NUM_LEVELS * k::C_NCOLS;
-constexpr int CHS_TAB_DOUBLES = CHS_TAB_INV_N + CHS_MAX_DRONES + 1;
+constexpr int CHS_TAB_APPROACH = CHS_TAB_INV_N + CHS_MAX_DRONES + 1;   // 5 / (SPEED_LIMIT / ctrl_freq + 1e-6)  (CattleAviary.py:253-256)
+constexpr int CHS_TAB_INV_M = CHS_TAB_APPROACH + 1;                    // 1 / num_cattle
+constexpr int CHS_TAB_DOUBLES = CHS_TAB_INV_M + 1;
 
 template <typename T> __device__ __forceinline__ T curr(const double* ct, int level, int col) { return T(ct[level * k::C_NCOLS + col]); }
 
@@ -19,17 +21,19 @@ template <typename T> __device__ __forceinline__ T simple_spacing(T r, T desired
   const T tol = desired * tolfrac;
   const T lo = desired - tol, hi = desired + tol;
   if (lo <= r && r <= hi) return T(1);
-  if (r < lo) return T(-1) + (r / lo) * T(2);
-  if (r > hi) return T(1) - ((r - hi) / (T(7.0) - hi)) * T(2);
+  // quotients through Mth::fdiv (MUFU reciprocal in the float build, exact in the double build): the shape is in [-1, 1]
+  if (r < lo) return T(-1) + Mth<T>::fdiv(r, lo) * T(2);
+  if (r > hi) return T(1) - Mth<T>::fdiv(r - hi, T(7.0) - hi) * T(2);
   return T(-1);
 }
 
 // CattleAviary.DroneSpacingRewardFunction (:630-667)
 template <typename T> __device__ __forceinline__ T complex_spacing(T r, T d_star) {
-  const T zz = (r - d_star) / T(0.4 + 1e-9);
+  // divisions by constants are multiplications by the reciprocal (one rounding apart from the reference's quotient)
+  const T zz = (r - d_star) * T(1.0 / (0.4 + 1e-9));
   const T gauss = Mth<T>::exp(T(-0.5) * zz * zz);
-  const T coll = (r < T(0.3)) ? T(-1.0) * (T(1.0) - (r / T(0.3 + 1e-9))) : T(0);
-  const T pull = (r > T(1.5)) ? T(-0.3) * (r - T(1.5)) / T(5.0 - 1.5) : T(0);
+  const T coll = (r < T(0.3)) ? T(-1.0) * (T(1.0) - (r * T(1.0 / (0.3 + 1e-9)))) : T(0);
+  const T pull = (r > T(1.5)) ? T(-0.3) * (r - T(1.5)) * T(1.0 / (5.0 - 1.5)) : T(0);
   return gauss + coll + pull + T(0.1) * (T(1) - Mth<T>::abs(r - d_star));
 }
 
@@ -37,8 +41,8 @@ template <typename T> __device__ __forceinline__ T complex_spacing(T r, T d_star
 template <typename T> __device__ __forceinline__ T cattle_spacing(T r) {
   if (r <= T(k::SP_R0)) {
     const T a = r - T(k::SP_D);
-    return T(k::SP_A) * Mth<T>::exp(-(a * a) / T(2 * k::SP_C * k::SP_C)) -
-           T(k::SP_B) * Mth<T>::exp(-(r * r) / T(2 * k::SP_K * k::SP_K));
+    return T(k::SP_A) * Mth<T>::exp(-(a * a) * T(1.0 / (2 * k::SP_C * k::SP_C))) -
+           T(k::SP_B) * Mth<T>::exp(-(r * r) * T(1.0 / (2 * k::SP_K * k::SP_K)));
   }
   // g(r0)/exp(-lam*r0) * exp(-lam*r); the prefactor is a constant of the shape parameters
   return T(2.662959707043491) * Mth<T>::exp(T(-k::SP_LAM) * r);

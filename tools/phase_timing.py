@@ -19,7 +19,7 @@ env = pkg.CattleHerdingBatchedEnv(E, num_drones=N, num_cattle=M, fixed_num_drone
                                   device=0, envs_per_block=G, threads_per_block=TH)
 env.reset()
 grid = (E + G - 1) // G
-clk = torch.zeros((grid, 16), dtype=torch.int64, device="cuda")
+clk = torch.zeros((grid, 32), dtype=torch.int64, device="cuda")
 acts = [torch.rand((E, N, 4), device="cuda") * 2 - 1 for _ in range(8)]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for i in range(40):
@@ -45,3 +45,21 @@ for n, v in zip(names, acc / R):
 print(f"  sum {acc.sum() / R:.0f} cyc")
 c = clk.cpu().numpy().astype(np.float64)
 print("  last step, p3 detail: barrier->loop %.0f, loop %.0f, after loop->stamp7 %.0f" % ((c[:, 13] - c[:, 6]).mean(), (c[:, 14] - c[:, 13]).mean(), (c[:, 7] - c[:, 14]).mean()))
+
+def span(a, b):
+    return (c[:, b] - c[:, a]).mean()
+print("  p1 detail: start->action/PID done %.0f, substeps+euler %.0f, stores %.0f" % (span(2, 16), span(16, 17), span(17, 3)))
+print("  p2 detail: neighbours %.0f, cattle obs loop %.0f, herd finish %.0f, winding %.0f" % (span(4, 19), span(19, 20), span(20, 21), span(21, 5)))
+print("  p3 detail: reward->stats done %.0f, env stores %.0f, bulk issue %.0f" % (span(8, 22), span(22, 23), span(23, 9)))
+tot = c[:, 12] - c[:, 0]
+p5 = c[:, 12] - c[:, 11]
+p3s = c[:, 9] - c[:, 8]
+busy = p5 > np.median(p5) * 1.5 + 200
+print("  last step: CTA total cycles min/median/p90/max = %.0f / %.0f / %.0f / %.0f" % (tot.min(), np.median(tot), np.percentile(tot, 90), tot.max()))
+print("  CTAs with a long p5 (reset): %d of %d; p5 %.0f vs %.0f cyc; p3 stores+stats %.0f vs %.0f; total %.0f vs %.0f" % (
+    busy.sum(), len(busy), p5[busy].mean() if busy.any() else 0, p5[~busy].mean(), p3s[busy].mean() if busy.any() else 0, p3s[~busy].mean(),
+    tot[busy].mean() if busy.any() else 0, tot[~busy].mean()))
+g0, g1 = c[:, 30], c[:, 31]
+t0 = g0.min()
+print("  last step, global timer [us] from the first CTA's start: CTA starts median %.2f / max %.2f; CTA ends min %.2f / median %.2f / max %.2f; CTA duration median %.2f" % (
+    np.median(g0 - t0) / 1e3, (g0 - t0).max() / 1e3, (g1 - t0).min() / 1e3, np.median(g1 - t0) / 1e3, (g1 - t0).max() / 1e3, np.median(g1 - g0) / 1e3))

@@ -4,7 +4,7 @@ import rl_cattle_herding_b200 as pkg
 E, G, TH, N, M = 4096, 8, 128, 3, 20
 env = pkg.CattleHerdingBatchedEnv(E, num_drones=N, num_cattle=M, fixed_num_drones=N, spawn_table=pkg.spawn.generate(100, M), device=0, envs_per_block=G, threads_per_block=TH)
 env.reset()
-clk = torch.zeros(((E + G - 1) // G, 16), dtype=torch.int64, device="cuda")
+clk = torch.zeros(((E + G - 1) // G, 32), dtype=torch.int64, device="cuda")
 acts = [torch.rand((E, N, 4), device="cuda") * 2 - 1 for _ in range(8)]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 def run(tag, n=40):
