@@ -61,12 +61,16 @@ class BaseAviary:
         self.is_evaluating = False
         self.step_counter = 0
         self._device = self.sim.device
+        from .telemetry import EvaluationLog
+        self._eval = EvaluationLog(self.sim, 0)
+        self.eval_system = self._eval              # the reference's attribute name (BaseAviary.py:124)
 
     # ---- gymnasium contract -----------------------------------------------------------------------------
     def reset(self, seed=None, options=None):
         """BaseAviary.reset (:280-331).  Like the reference, `seed` does not reseed the environment."""
         obs = self.sim.reset()
         self._refresh()
+        self._eval.on_reset()
         return obs[0].cpu().numpy(), self._computeInfo()
 
     def step(self, action):
@@ -77,6 +81,10 @@ class BaseAviary:
         obs, rew, term, trunc = self.sim.step(a.to(self._device))
         out = (obs[0].cpu().numpy(), float(rew[0].item()), bool(term[0].item()), bool(trunc[0].item()), self._computeInfo())
         self._refresh()
+        self._eval.on_step()                       # update_evaluation_metrics runs every step (BaseAviary.py:462)
+        # evaluation_episode_trigger: only an evaluating env whose episode hit the time limit (CattleAviary.py:545-550)
+        if self.is_evaluating and out[3] and self.step_counter / self.CTRL_FREQ > self.EPISODE_LEN_SEC:
+            self._eval.on_episode_end()
         return out
 
     def render(self, mode="human", close=False):
@@ -100,9 +108,10 @@ class BaseAviary:
     def getDroneIds(self):
         return np.arange(1, self.NUM_DRONES + 1)
 
-    def evaluation_save(self):
-        """The reference pickles a host-side trajectory log (utils/evaluation.py:73-94); telemetry here lives in
-        the device-side statistics vector."""
+    def evaluation_save(self, save_path="evaluation_data.pkl"):
+        """`evaluator.save_evaluation_data` (utils/evaluation.py:73-94): pickles the trajectory log in the reference's
+        schema (telemetry.EvaluationLog) and returns the device-side episode statistics vector as well."""
+        self._eval.save(save_path)
         return self.sim.stats()
 
     def _getDroneStateVector(self, nth_drone):

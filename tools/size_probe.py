@@ -9,7 +9,7 @@ import rl_cattle_herding_b200 as pkg  # noqa: E402
 from launch_sweep import time_shape  # noqa: E402
 
 G, TH = int(sys.argv[1]), int(sys.argv[2])
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+flush = None if os.environ.get("NO_FLUSH") else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for E in [int(x) for x in sys.argv[3:]]:
     env = pkg.CattleHerdingBatchedEnv(E, num_drones=3, num_cattle=20, ctrl_freq=30, fixed_num_drones=3,
                                       spawn_table=pkg.spawn.generate(100, 20, seed=0), device=0, seed=1,
