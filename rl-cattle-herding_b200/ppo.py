@@ -143,7 +143,9 @@ class DevicePPO:
         self.policy = MlpActorCritic(self.obs_dim, self.act_dim, base["hidden"], base["log_std_init"]).to(dev)
         import torch.distributed as dist
         multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        self.cuda_graphs = (not multi) if cuda_graphs is None else bool(cuda_graphs)
+        self.cuda_graphs = (not multi) if cuda_graphs is None else bool(cuda_graphs)     # minibatch update as a graph
+        # the rollout has no collective in it (envs are sharded, nothing is exchanged): its graph is safe on every rank
+        self.graph_rollout = True if cuda_graphs is None else bool(cuda_graphs)
         self.opt = torch.optim.Adam(self.policy.parameters(), lr=base["learning_rate"], eps=1e-5, capturable=self.cuda_graphs)
         T, B = self.n_steps, self.B
         f = dict(dtype=torch.float32, device=dev)
@@ -201,7 +203,7 @@ class DevicePPO:
         env = self.env
         if self._obs is None:
             self._obs = self._flat_obs(env.reset()).clone()
-        if self.cuda_graphs:
+        if self.graph_rollout:
             if self._g_roll is None:
                 side = torch.cuda.Stream(device=env.device)
                 side.wait_stream(torch.cuda.current_stream(env.device))
