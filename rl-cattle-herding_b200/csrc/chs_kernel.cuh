@@ -279,8 +279,23 @@ __device__ __forceinline__ void spawn_xy(int d, int n, T& x, T& y) {
 // `parts` selects what this call does (bit 0 cows, bit 1 drones, bit 2 observation): the three are independent, so the
 // fused kernel hands them to different warps.
 enum ResetPart { RESET_COWS = 1, RESET_DRONES = 2, RESET_OBS = 4, RESET_ALL = 7 };
+// The only state a rebuild reads is the PID memory of the drone slots (fields E, F, G); `PidPre` lets the caller issue
+// those loads before it knows n / row / epi, so that their DRAM round trip overlaps the env-scalar one.
+template <typename T> struct PidPre { typename VT<T>::v4 e, f, g; };
 template <typename T>
-__device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, int row, int epi, int lane, int parts) {
+__device__ __forceinline__ PidPre<T> reset_preload(const KArgs<T>& a, int e, int lane) {
+  PidPre<T> r;
+  r.e = r.f = r.g = mk4<T>(0, 0, 0, 0);
+  if (lane < a.p.D) {
+    const size_t st = (size_t)a.p.D * a.p.E;
+    const typename VT<T>::v4* base = a.drone + (size_t)lane * a.p.E + e;
+    r.e = base[F_E * st]; r.f = base[F_F * st]; r.g = base[F_G * st];
+  }
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, int row, int epi, int lane, int parts,
+                                               const PidPre<T>& pid) {
   const KParams& p = a.p;
   const unsigned full = 0xffffffffu;
   const int E = p.E, D = p.D, M = p.M, L = p.L;
@@ -292,19 +307,28 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
     const auto xy = srow[j];
     uint32_t c[4] = {(uint32_t)(p.env_id_offset + e), (uint32_t)epi, (uint32_t)j, (uint32_t)TAG_COW};
     philox4x32_10(c, p.seed_lo, p.seed_hi);
-    T sn, cs;
-    Mth<T>::sincospi(T(2.0 * u01_24(c[1]) - 1.0), &sn, &cs);
+    T sn, cs, ang;
+    // 2u - 1 with u = k / 2^24: exact in float as well ((k - 2^23) / 2^23 has a 24-bit numerator), so the float build
+    // skips the double arithmetic and lands on the same bits
+    if (sizeof(T) == 4) ang = T((float)(c[1] >> 8) * 1.1920928955078125e-07f - 1.0f);
+    else ang = T(2.0 * u01_24(c[1]) - 1.0);
+    Mth<T>::sincospi(ang, &sn, &cs);
     a.cpos[(size_t)j * E + e] = xy;
     a.cvel[(size_t)j * E + e] = mk2<T>(T(k::MAX_VEL_CATTLE) * cs, T(k::MAX_VEL_CATTLE) * sn);
   }
-  if (parts & RESET_DRONES) for (int d = lane; d < D; d += 32) {   // drones: every slot's kinematics zeroed, PID kept
-    DroneState<T> ds;
-    load_drone<T>(a, d, e, ds);
-#pragma unroll
-    for (int q = 0; q < 3; ++q) { ds.p[q] = 0; ds.v[q] = 0; ds.w[q] = 0; ds.rpy[q] = 0; ds.av[q] = 0; }
-    ds.q[0] = ds.q[1] = ds.q[2] = ds.q[3] = 0;
-    if (d < n) { spawn_xy<T>(d, n, ds.p[0], ds.p[1]); ds.p[2] = T(k::TARGET_ALT); ds.q[3] = T(1); }
-    store_drone<T>(a, d, e, ds);
+  if ((parts & RESET_DRONES) && lane < D) {   // drones (D <= 12 slots, one lane each): kinematics zeroed, PID kept
+    const int d = lane;
+    T px = 0, py = 0, pz = 0, qw = 0;
+    if (d < n) { spawn_xy<T>(d, n, px, py); pz = T(k::TARGET_ALT); qw = T(1); }
+    const size_t st = (size_t)D * E;
+    typename VT<T>::v4* base = a.drone + (size_t)d * E + e;
+    base[F_A * st] = mk4<T>(px, py, pz, 0);
+    base[F_B * st] = mk4<T>(0, 0, 0, qw);
+    base[F_C * st] = mk4<T>(0, 0, 0, 0);
+    base[F_D * st] = mk4<T>(0, 0, 0, 0);
+    base[F_E * st] = mk4<T>(pid.e.x, pid.e.y, pid.e.z, 0);
+    base[F_F * st] = mk4<T>(pid.f.x, pid.f.y, pid.f.z, 0);
+    base[F_G * st] = mk4<T>(pid.g.x, pid.g.y, pid.g.z, 0);
     a.rpm[(size_t)d * E + e] = mk4<T>(0, 0, 0, 0);
   }
   if (a.obs == nullptr || !(parts & RESET_OBS)) return;
@@ -368,6 +392,7 @@ __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
   const int count = *a.done_count;
   for (int i = gw; i < count; i += nwarps) {
     const int e = a.done_list[i];
+    const PidPre<T> pid = reset_preload<T>(a, e, lane);
     int n = 0, row = 0, epi = 0;
     if (lane == 0) {
       const int4 ei = a.envi[e];
@@ -381,7 +406,7 @@ __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
       a.epret[e] = 0.0;
     }
     n = __shfl_sync(full, n, 0); row = __shfl_sync(full, row, 0); epi = __shfl_sync(full, epi, 0);
-    reset_env_warp<T>(a, e, n, row, epi, lane, RESET_ALL);
+    reset_env_warp<T>(a, e, n, row, epi, lane, RESET_ALL, pid);
   }
 }
 
@@ -1005,8 +1030,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     __syncthreads();
     const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
     for (int i = warp; i < 3 * nd; i += nwarp) {
-      const int g = s.dlist[i / 3];
-      reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, 1 << (i % 3));
+      const int g = s.dlist[i / 3], part = 1 << (i % 3);
+      PidPre<T> pid;
+      if (part == RESET_DRONES) pid = reset_preload<T>(a, e0 + g, lane);
+      reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, part, pid);
     }
   }
   if (!FULL || p.bulk_ok) bulk_wait_read();       // shared memory must outlive the pending bulk reads
