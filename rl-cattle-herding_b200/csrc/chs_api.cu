@@ -61,6 +61,8 @@ struct ChsHandle {
   int threads, smem;
   int reg_variant;            // 0 auto, 1 latency (128 regs), 2 occupancy (64 regs)
   bool spawn_set;
+  unsigned* amask;       // alpha-term in-range masks per spawn row (alpha_mask_kernel)
+  bool amask_ok;         // every env's cattle sit on its spawn row: a full reset happened and nobody injected positions
   // device-side buffers of the host path (allocated on first use)
   float *d_actions, *d_obs, *d_reward, *d_termobs;
   uint8_t *d_term, *d_trunc, *d_mask;
@@ -264,7 +266,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
 extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
-  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count,
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count, h->amask,
                   h->d_actions, h->d_obs, h->d_small, h->d_termobs, h->d_mask};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_small) cudaFreeHost(h->h_small);
@@ -306,6 +308,17 @@ extern "C" int chs_set_spawn_table(ChsHandle* h, const double* xy, int32_t n_sim
   for (int e = 0; e < h->E; ++e) ei[e].w = (int)(((long long)h->kp.env_id_offset + e) % n_sims);
   CUDA_TRY(cudaMemcpy(h->envi, ei.data(), ei.size() * sizeof(int4), cudaMemcpyHostToDevice));
   h->spawn_set = true;
+  // who is within the alpha range of whom is a property of the spawn row (cattle do not move on the DYN path)
+  if (h->amask) { cudaFree(h->amask); h->amask = nullptr; }
+  h->amask_ok = false;                 // until the next full reset puts every herd on its row of the new table
+  const size_t words = (size_t)n_sims * h->kp.M * ((h->kp.M + 31) / 32);
+  if (h->kp.M > 0 && !getenv("CHS_NO_ALPHA_TABLE") && words * sizeof(unsigned) <= (64u << 20)) {
+    CUDA_TRY(cudaMalloc(&h->amask, words * sizeof(unsigned)));
+    const unsigned grid = (unsigned)(((size_t)n_sims * h->kp.M + 255) / 256);
+    if (h->f64) alpha_mask_kernel<double><<<grid, 256>>>((const double2*)h->spawn, n_sims, cows_per_sim, h->kp.M, h->amask);
+    else        alpha_mask_kernel<float><<<grid, 256>>>((const float2*)h->spawn, n_sims, cows_per_sim, h->kp.M, h->amask);
+    CUDA_TRY(cudaDeviceSynchronize());
+  }
   return CHS_OK;
 }
 
@@ -344,6 +357,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
   a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats; a.tab = h->tab;
+  a.amask = (h->amask_ok && !h->kp.cattle_integrate) ? h->amask : nullptr;
   a.own2 = (typename VT<T>::v4*)h->own2; a.pos0 = (const typename VT<T>::v4*)h->pos0;
   a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd; a.dbg_clock = h->dbg_clock;
   return a;
@@ -359,6 +373,7 @@ static int launch_reset(ChsHandle* h, const uint8_t* mask_dev, float* obs_dev, c
   const int grid = ngroups < 148 * 8 ? ngroups : 148 * 8;
   reset_kernel<T><<<grid, h->threads, h->smem, st>>>(a);
   CUDA_TRY(cudaGetLastError());
+  if (!mask_dev && h->amask) h->amask_ok = true;     // every herd now sits on its spawn row (stream-ordered before later steps)
   return CHS_OK;
 }
 

@@ -41,21 +41,34 @@ __device__ __forceinline__ void lattice_term(T dx, T dy, T dpx, T dpy, T sigma_r
 // different envs, so the in-range set differs per lane: a cheap uniform pass collects the in-range cows of a
 // 32-cow chunk in a bit mask, then every lane walks only its own set bits (a NaN distance stays in the set and
 // propagates like in the reference).
+// In-range set of cow i inside the 32-cow chunk starting at j0, as a bit mask (bit jj = cow j0 + jj; cow i itself
+// excluded).  `pos(j)` returns the xy of cow j.  One definition for the step kernel and for the per-spawn-row table.
+template <typename T, typename Pos>
+__device__ __forceinline__ unsigned alpha_chunk_mask(Pos pos, typename VT<T>::v2 qi, int i, int j0, int M) {
+  const int jn = (M - j0 < 32) ? (M - j0) : 32;
+  unsigned mask = 0;
+  for (int jj = 0; jj < jn; ++jj) {
+    const auto qj = pos(j0 + jj);
+    const T dx = qj.x - qi.x, dy = qj.y - qi.y;
+    if (!(dx * dx + dy * dy >= T(k::ALPHA_RANGE * k::ALPHA_RANGE))) mask |= 1u << jj;
+  }
+  if (i >= j0 && i < j0 + 32) mask &= ~(1u << (i - j0));
+  return mask;
+}
+
+// `mwords` (nullable): the in-range masks of cow i for this env's spawn row, one word per 32-cow chunk, tabulated by
+// chs_set_spawn_table.  Cattle never move on the DYN path, so who is within 1.2 m of whom is a property
+// of the spawn row; with the table the O(M^2) distance pass -- most of the herd update's instructions -- becomes M loads.
 template <typename T>
 __device__ __forceinline__ void alpha_term(const typename VT<T>::v2* s_cpos, const typename VT<T>::v2* s_cvel,
-                                           int i, int g, int G, int M, T& ux, T& uy) {
+                                           int i, int g, int G, int M, const unsigned* __restrict__ mwords, T& ux, T& uy) {
   const auto qi = s_cpos[i * G + g];
   const auto pi = s_cvel[i * G + g];
   T gx = 0, gy = 0, cx = 0, cy = 0;
   for (int j0 = 0; j0 < M; j0 += 32) {
-    const int jn = (M - j0 < 32) ? (M - j0) : 32;
-    unsigned mask = 0;
-    for (int jj = 0; jj < jn; ++jj) {
-      const auto qj = s_cpos[(j0 + jj) * G + g];
-      const T dx = qj.x - qi.x, dy = qj.y - qi.y;
-      if (!(dx * dx + dy * dy >= T(k::ALPHA_RANGE * k::ALPHA_RANGE))) mask |= 1u << jj;
-    }
-    if (i >= j0 && i < j0 + 32) mask &= ~(1u << (i - j0));
+    unsigned mask;
+    if (mwords) mask = __ldg(mwords + (j0 >> 5));
+    else mask = alpha_chunk_mask<T>([&](int j) { return s_cpos[j * G + g]; }, qi, i, j0, M);
     while (mask) {
       const int j = j0 + __ffs(mask) - 1;
       mask &= mask - 1;

@@ -383,6 +383,18 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
   }
 }
 
+// Alpha-term in-range masks of every cow of every spawn row (one thread per (row, cow)), same expression as the step kernel.
+template <typename T>
+__global__ void __launch_bounds__(256) alpha_mask_kernel(const typename VT<T>::v2* spawn, int n_sims, int stride, int M, unsigned* out) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_sims * M) return;
+  const int row = idx / M, i = idx - row * M, nch = (M + 31) >> 5;
+  const typename VT<T>::v2* r = spawn + (size_t)row * stride;
+  const auto qi = r[i];
+  for (int c = 0; c < nch; ++c)
+    out[(size_t)idx * nch + c] = alpha_chunk_mask<T>([&](int j) { return r[j]; }, qi, i, c * 32, M);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
   const KParams& p = a.p;
@@ -559,7 +571,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       if (t < G) {
         int n = 0;
         if (env_lane) { n = pre_i.z; fl = (((pre_i.y + 1) & 1) == 0); }
-        s.n[t] = n; s.herd[t] = 0; s.done[t] = 0; s.level[t] = pre_j.x;
+        s.n[t] = n; s.herd[t] = 0; s.done[t] = 0; s.level[t] = pre_j.x; s.row[t] = pre_i.w;   // row: spawn row of the running episode
       }
       const unsigned m = __ballot_sync(0xffffffffu, fl);
       if (fl) s.flist[__popc(m & ((1u << t) - 1u))] = t;
@@ -672,7 +684,8 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       for (int it = w; it < nact * M; it += nw) {
         const int g = s.flist[it % nact], i = it / nact;
         T ux, uy;
-        alpha_term<T>(s.cpos, s.cvel, i, g, G, M, ux, uy);
+        const unsigned* mw = a.amask ? a.amask + ((size_t)s.row[g] * M + i) * ((M + 31) >> 5) : nullptr;
+        alpha_term<T>(s.cpos, s.cvel, i, g, G, M, mw, ux, uy);
         s.u[i * G + g] = mk2<T>(ux, uy);
       }
     }

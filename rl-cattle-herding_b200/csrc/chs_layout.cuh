@@ -57,6 +57,7 @@ template <typename T> struct KArgs {
   double2* envf;
   double* epret;
   const typename VT<T>::v2* spawn;   // [n_sims][spawn_stride]
+  const unsigned* amask;             // nullable [n_sims][M][ceil(M/32)]: alpha-term in-range masks per spawn row (chs_flock.cuh)
   double* stats;                     // [CHS_NUM_STATS]
   const double* tab;                 // [CHS_TAB_DOUBLES] curriculum rows + 1/n (chs_task.cuh)
   // per-call

@@ -64,3 +64,33 @@ def test_edge_shapes_against_oracle(case, mode):
             assert bool(term[e]) == oterm and bool(trunc[e]) == otrunc, (step, e)
     assert worst < 1e-6, worst          # float64 build; the obs / reward tensors are float32
     env.close()
+
+
+@pytest.mark.parametrize("shape", [(3, 20), (8, 100), (4, 33)], ids=lambda s: "D%d_M%d" % s)
+def test_alpha_range_table_equals_computed_ranges(shape, monkeypatch):
+    """The per-spawn-row table of alpha-term in-range masks (built by chs_set_spawn_table) against the distance pass it
+    replaces: same herd velocities, bit for bit, over free-running steps with resets in between."""
+    import rl_cattle_herding_b200 as pkg
+    D, M = shape
+    E = 64
+    table = pkg.spawn.generate(6, M, seed=4)
+
+    def make():
+        return pkg.CattleHerdingBatchedEnv(E, num_drones=D, num_cattle=M, ctrl_freq=30, fixed_num_drones=D, spawn_table=table,
+                                           device=0, seed=9, auto_reset=True)
+    with_table = make()
+    monkeypatch.setenv("CHS_NO_ALPHA_TABLE", "1")       # read by chs_set_spawn_table
+    computed = make()
+    monkeypatch.delenv("CHS_NO_ALPHA_TABLE")
+    for env in (with_table, computed):
+        env.reset()
+    gen = torch.Generator("cuda").manual_seed(2)
+    for t in range(40):
+        act = torch.rand((E, D, 4), device="cuda", generator=gen) * 2 - 1
+        a = [x.clone() for x in with_table.step(act)]
+        b = computed.step(act)
+        assert all(torch.equal(x, y) for x, y in zip(a, b)), t
+    sa, sb = with_table.get_state(), computed.get_state()
+    assert np.array_equal(sa["cattle_vel"], sb["cattle_vel"]) and np.array_equal(sa["cattle_pos"], sb["cattle_pos"])
+    assert with_table.stats()[0] > 0          # episodes ended and restarted on other spawn rows along the way
+    with_table.close(); computed.close()
