@@ -200,21 +200,34 @@ def time_steps(env, torch, action_pool, n_steps, flush_buf, stream_sync=True):
     return [s.elapsed_time(e) for s, e in zip(starts, ends)]   # ms each
 
 
-def autotune_launch(env, torch, action_pool, flush_buf, candidates, reps=24, modes=("fused",)):
-    """Untimed: picks (envs per CTA, threads per CTA, step mode) by median step time.  Returns (ms, G, threads, mode)."""
-    best = None
-    for mode in modes:
+def autotune_launch(env, torch, action_pool, flush_buf, candidates, reps=12, modes=("fused",), final_reps=40):
+    """Untimed: picks (envs per CTA, threads per CTA, step mode).  Shapes are a few percent apart and a short sample is
+    noisy, so a quick pass ranks all candidates and the three best are measured again, longer and interleaved (two
+    rounds each), before one is chosen by trimmed mean.  Returns (ms, G, threads, mode)."""
+    def sample(mode, g, th, n):
         env.set_step_mode(mode)
+        env.set_launch(g, th)
+        time_steps(env, torch, action_pool, 3, flush_buf)
+        return time_steps(env, torch, action_pool, n, flush_buf)
+
+    def trimmed(ts):
+        ts = sorted(ts)
+        return float(np.mean(ts[: max(1, (3 * len(ts)) // 4)]))
+
+    ranked = []
+    for mode in modes:
         for g, th in candidates:
             try:
-                env.set_launch(g, th)
+                ranked.append((trimmed(sample(mode, g, th, reps)), g, th, mode))
             except RuntimeError:
                 continue
-            time_steps(env, torch, action_pool, 3, flush_buf)
-            ts = sorted(time_steps(env, torch, action_pool, reps, flush_buf))
-            ms = float(np.mean(ts[: max(1, (3 * len(ts)) // 4)]))     # trimmed mean: shapes are a few percent apart
-            if best is None or ms < best[0]:
-                best = (ms, g, th, mode)
+    ranked.sort()
+    finalists = ranked[:3]
+    acc = {f[1:]: [] for f in finalists}
+    for _ in range(2):
+        for _, g, th, mode in finalists:
+            acc[(g, th, mode)] += sample(mode, g, th, final_reps // 2)
+    best = min((trimmed(v), k[0], k[1], k[2]) for k, v in acc.items())
     env.set_step_mode(best[3])
     env.set_launch(best[1], best[2])
     return best
