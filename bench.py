@@ -293,6 +293,21 @@ def run_cuda_arm(args):
     ms_per_step = total_ms / K
     value = world * E * K / (total_ms * 1e-3)
 
+    # supplementary, untimed: the same step as CUPTI sees it (kernel activity records of 20 more flushed launches), i.e.
+    # without what an event pair around a single launch adds at both ends
+    activity_ms = None
+    if rank == 0:
+        try:
+            from torch.profiler import ProfilerActivity, profile
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                time_steps(env, torch, action_pool, 20, flush_buf)
+            ours = [e.time_range.elapsed_us() for e in prof.events()
+                    if e.device_type == torch.autograd.DeviceType.CUDA and "chs::" in e.name]
+            if ours:
+                activity_ms = sum(ours) / 20 * 1e-3
+        except Exception:  # noqa: BLE001  (profiler not available: the field stays null)
+            activity_ms = None
+
     line = None
     if rank == 0:
         dims = env.dims
@@ -320,7 +335,8 @@ def run_cuda_arm(args):
                          "traffic": recorded_traffic(wl_key), "bytes_per_env_step": bytes_env,
                          "bytes_per_launch": bytes_env * E, "peak_source": peak_src,
                          "kernel": "chs::step_kernel<float>" if tuned[3] == "fused" else "chs::drone_kernel<float> + chs::step_kernel<float> + chs::reset_list_kernel<float> (one control step)",
-                         "kernel_ms": float(np.mean(per_step_ms))},
+                         "kernel_ms": float(np.mean(per_step_ms)),
+                         "kernel_activity_ms_cupti": activity_ms},
             "clocks": clocks.summary(),
             "episodes": {"finished": float(stats[0].item()), "mean_length": float(stats[2].item() / max(1.0, stats[0].item())),
                          "mean_return": float(stats[1].item() / max(1.0, stats[0].item())), "non_finite": float(stats[9].item())},
