@@ -198,6 +198,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   h->step_mode = prm->reserved0;
   { const char* v = getenv("CHS_SMEM_PAD"); h->knob_smem_pad = v ? atoi(v) : 0; }
   h->knob_full = getenv("CHS_FULL_KERNEL") != nullptr;
+  kp.early_ok = getenv("CHS_NO_EARLY") ? 0 : 1;
   h->knob_inline_reset = getenv("CHS_INLINE_RESET") != nullptr;
   kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;

@@ -526,6 +526,13 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       for (int i = 0; i < 4; ++i) if (i < p.A) act0[i] = ap[i];
     }
   }
+  // Early start of the drone chain: with a single drone warp (warp 0) and other warps to do the staging, warp 0 only
+  // ARRIVES at the barrier that closes phase 0 and goes straight into its serial chain as soon as its own loads land;
+  // it neither stages the herd nor waits for the copies of the others.  It meets the staging warps again on named
+  // barrier 1 just before its first shared-memory write (the staging area has to be zeroed by then).
+  const bool early = !SPLIT && p.early_ok && ndt == 32 && nt > 32 && (!FULL || (p.cp_ok && !(p.aero_flags & 4)));
+  const int sw0 = early ? ndt : 0;           // first thread that takes part in the staging loops
+  const int snt = nt - sw0, sw = t - sw0;    // sw < 0: exempt
   {
     using V2 = typename VT<T>::v2;
     if (!FULL || p.cp_ok) {
@@ -534,7 +541,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       constexpr int EPC = 16 / (int)sizeof(V2);            // envs per 16-byte chunk
       const int cpr = G / EPC;                             // chunks per cow row
       const int nchunk = 2 * M * cpr;
-      for (int it = t; it < nchunk; it += nt) {
+      if (sw >= 0) for (int it = sw; it < nchunk; it += snt) {
         const int arr = (it >= M * cpr) ? 1 : 0;
         const int r = it - arr * M * cpr;
         const int j = r / cpr, c = r - j * cpr;
@@ -553,12 +560,14 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       }
     }
     // curriculum table: 76 chunks of 16 bytes
-    for (int it = t; it < 76; it += nt) cp_async16(s.ctab + 2 * it, a.tab + 2 * it, 16);
+    if (sw >= 0) for (int it = sw; it < 76; it += snt) cp_async16(s.ctab + 2 * it, a.tab + 2 * it, 16);
     cp_async_commit();
     const int nq = (G * p.stage_stride) >> 2;
     float4* st4 = reinterpret_cast<float4*>(s.stage);
-    for (int i = t; i < nq; i += nt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = t; i < (p.zero_bytes >> 4); i += nt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (sw >= 0) {
+      for (int i = sw; i < nq; i += snt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = sw; i < (p.zero_bytes >> 4); i += snt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     if (FULL && !p.cp_ok) {
       for (int it = t; it < M * G; it += nt) {
         const int g = it & (G - 1), j = it >> lg, e = e0 + g;
@@ -580,7 +589,17 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     cp_async_wait_all();
   }
   CHS_STAMP(1);
-  __syncthreads();
+  if (early) {
+    if (t < ndt) {
+      __syncwarp();
+      asm volatile("bar.arrive 0, %0;" ::"r"(nt) : "memory");
+    } else {
+      asm volatile("bar.sync 0, %0;" ::"r"(nt) : "memory");
+      asm volatile("bar.arrive 1, %0;" ::"r"(nt) : "memory");
+    }
+  } else {
+    __syncthreads();
+  }
   CHS_STAMP(2);
   // Observation traffic is 3/4 constant zeros (rows >= D of the (R, L) image).  They leave NOW, from the CTA's zero
   // block, issued by the last warp: the write drains while the SMs compute instead of queueing behind the live rows at
@@ -627,6 +646,8 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       }
     }
   } else if (t < ndt) {
+    DroneState<T> held;            // early mode: the one item of this thread, parked until the staging area is ready
+    int held_it = -1;
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       if (e < E && d < s.n[g]) {
@@ -658,12 +679,25 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         CHS_STAMP(17);
         store_drone<T>(a, d, e, ds);
         a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
+        if (early) { held = ds; held_it = it; continue; }      // DG <= 32: one item per thread
         s.dpos[it] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], T(0));
         // own-state part of the obs row (BaseRLAviary.py:286-297): z, rpy, vel, ang_v
         float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
         row[0] = (float)ds.p[2];
 #pragma unroll
         for (int i = 0; i < 3; ++i) { row[1 + i] = (float)ds.rpy[i]; row[4 + i] = (float)ds.v[i]; row[7 + i] = (float)ds.av[i]; }
+      }
+    }
+    if (early) {
+      __syncwarp();
+      asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");     // the staging warps arrived here long ago
+      if (held_it >= 0) {
+        const int g = held_it & (G - 1), d = held_it >> lg;
+        s.dpos[held_it] = mk4<T>(held.p[0], held.p[1], held.p[2], T(0));
+        float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
+        row[0] = (float)held.p[2];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { row[1 + i] = (float)held.rpy[i]; row[4 + i] = (float)held.v[i]; row[7 + i] = (float)held.av[i]; }
       }
     }
   }

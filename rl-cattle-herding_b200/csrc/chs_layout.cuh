@@ -41,6 +41,7 @@ struct KParams {
   int split;             // 1: drones are integrated by drone_kernel, step_kernel does the rest
   int bulk_ok;           // observations leave through bulk (TMA) stores: R*L*4 and the staging stride are multiples of 16 B
   int zero_bytes;        // size of the shared zero block = R*L*4 - min(stage_stride*4, R*L*4)
+  int early_ok;          // warp 0 may start its drone chain before the other warps finish staging (CHS_NO_EARLY=1 clears it)
   uint32_t seed_lo, seed_hi;
 };
 
