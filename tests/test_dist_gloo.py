@@ -63,3 +63,45 @@ def test_bench_reference_arm_other_ranks_are_silent():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                          capture_output=True, text=True, env=env, timeout=120)
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+GRAD_WORKER = textwrap.dedent("""
+    import os, sys, json
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, %r)
+    from rl_cattle_herding_b200 import ppo
+    dist.init_process_group("gloo")
+    rank, ws = dist.get_rank(), dist.get_world_size()
+    torch.manual_seed(0)                                   # same weights on every rank
+    pol = ppo.MlpActorCritic(6, 2, (8, 8), -1.0)
+    torch.manual_seed(100 + rank)                          # different data per rank (its env shard)
+    obs, act = torch.randn(32, 6), torch.randn(32, 2)
+    mean, log_std = pol.dist(obs)
+    loss = -pol.log_prob(mean, log_std, act).mean() + pol.value(obs).pow(2).mean()
+    loss.backward()
+    local = torch.cat([p.grad.reshape(-1) for p in pol.parameters()]).clone()
+    ppo.average_gradients(list(pol.parameters()))
+    avg = torch.cat([p.grad.reshape(-1) for p in pol.parameters()])
+    both = [torch.zeros_like(local) for _ in range(ws)]
+    dist.all_gather(both, local)
+    expect = sum(both) / ws
+    if rank == 0:
+        print(json.dumps({"ws": ws, "err": float((avg - expect).abs().max()), "differs": float((both[0] - both[1]).abs().max())}))
+    dist.barrier()
+    dist.destroy_process_group()
+""")
+
+
+def test_learner_gradient_average_world_size_2(tmp_path):
+    """Per-GPU learners (ppo.average_gradients): every rank ends up with the mean of the ranks' gradients."""
+    script = tmp_path / "grad_worker.py"
+    script.write_text(GRAD_WORKER % ROOT)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29733", str(script)],
+                         capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    import json
+    d = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    assert d["ws"] == 2 and d["err"] < 1e-6 and d["differs"] > 1e-3
