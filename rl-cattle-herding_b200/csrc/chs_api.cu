@@ -255,7 +255,10 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   int G = prm->envs_per_block, threads = prm->threads_per_block;
   if (G == 0) {
     G = 32;
-    while (G > 1 && (smem_for(h, G) > 64 * 1024 || (num_envs + G - 1) / G < 2 * 148)) G >>= 1;
+    // not below two envs per CTA when that fits: one env per CTA cannot stage the herd with 16-byte async copies and
+    // falls to the full build of the kernel (same results up to fp32 contraction, but not bit for bit)
+    while (G > 2 && (smem_for(h, G) > 64 * 1024 || (num_envs + G - 1) / G < 2 * 148)) G >>= 1;
+    if (G == 2 && (num_envs < 2 || smem_for(h, 2) > 64 * 1024)) G = 1;
   }
   if (threads == 0) threads = (G * kp.M <= 256) ? 128 : 256;
   int rc = configure_launch(h, G, threads);
