@@ -143,7 +143,9 @@ class DevicePPO:
         self.policy = MlpActorCritic(self.obs_dim, self.act_dim, base["hidden"], base["log_std_init"]).to(dev)
         import torch.distributed as dist
         multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        self.cuda_graphs = (not multi) if cuda_graphs is None else bool(cuda_graphs)     # minibatch update as a graph
+        # minibatch update as a graph: single GPU only (capturing the NCCL gradient all-reduce inside it hung on 2 x B200
+        # with this torch / NCCL pair, so per-GPU learners run their update eagerly)
+        self.cuda_graphs = ((not multi) if cuda_graphs is None else bool(cuda_graphs)) and not multi
         # the rollout has no collective in it (envs are sharded, nothing is exchanged): its graph is safe on every rank
         self.graph_rollout = True if cuda_graphs is None else bool(cuda_graphs)
         self.opt = torch.optim.Adam(self.policy.parameters(), lr=base["learning_rate"], eps=1e-5, capturable=self.cuda_graphs)
@@ -212,7 +214,7 @@ class DevicePPO:
                 torch.cuda.current_stream(env.device).wait_stream(side)
                 torch.cuda.synchronize(env.device)
                 self._g_roll = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(self._g_roll):
+                with torch.cuda.graph(self._g_roll, capture_error_mode="thread_local"):
                     self._rollout_body()
             else:
                 self._g_roll.replay()
@@ -260,7 +262,8 @@ class DevicePPO:
         torch.cuda.synchronize(dev)
         self._g_upd = torch.cuda.CUDAGraph()
         self.opt.zero_grad(set_to_none=True)
-        with torch.cuda.graph(self._g_upd):
+        # thread-local capture mode: the NCCL watchdog thread of a multi-GPU job may touch the CUDA API meanwhile
+        with torch.cuda.graph(self._g_upd, capture_error_mode="thread_local"):
             self._minibatch_step(self._idx)
         with torch.no_grad():                       # undo the warm-up and the capture pass
             for p, q in zip(self._params, saved_p):
