@@ -1,8 +1,10 @@
 """Harness that runs the UNMODIFIED reference (`/root/reference/gym_pybullet_drones`) headless.
 
-TEST INFRASTRUCTURE ONLY.  Works only in the build container (the reference tree does not exist
-on the GPU box): it is used to (a) generate the golden fixtures under `tests/golden/` and (b)
-cross-check `oracle/cattle_oracle.py` directly against the reference.
+TEST INFRASTRUCTURE ONLY.  It is used to (a) generate the golden fixtures under `tests/golden/`, (b)
+cross-check `oracle/cattle_oracle.py` directly against the reference and (c) time the reference's own CPU
+code as the baseline arm of `bench.py`.  The reference tree is taken from `/root/reference` (build container)
+or, on the GPU box where that path does not exist, from the byte-for-byte staged copy `oracle/_ref`
+(`oracle/make_ref.py`, git-ignored, travels like libchs.so).
 
 How the reference is made importable:
   * `oracle/ref_harness/standins/` provides `pybullet`, `pybullet_data`, `gymnasium`
@@ -22,9 +24,19 @@ import sys
 
 import numpy as np
 
-REFERENCE_ROOT = "/root/reference"
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _STANDINS = os.path.join(_HERE, "standins")
+_STAGED = os.path.abspath(os.path.join(_HERE, "..", "_ref"))
+
+
+def _find_root():
+    for cand in (os.environ.get("CHS_REFERENCE_ROOT"), "/root/reference", _STAGED):
+        if cand and os.path.isdir(os.path.join(cand, "gym_pybullet_drones")):
+            return cand
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _find_root()
 
 
 def reference_available():
@@ -32,10 +44,26 @@ def reference_available():
 
 
 def _ensure_paths():
+    # stand-ins go to the END of sys.path: a real pybullet / gymnasium, where one is installed, wins
     if _STANDINS not in sys.path:
-        sys.path.insert(0, _STANDINS)
+        sys.path.append(_STANDINS)
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
+
+
+def third_party_kinds():
+    """Which pybullet / gymnasium the reference is running on: "stand-in" (oracle/ref_harness/standins) or
+    "real <version>".  Recorded next to every CPU number (VERDICT r1, weak #3)."""
+    _ensure_paths()
+    out = {}
+    for name in ("pybullet", "gymnasium"):
+        try:
+            mod = __import__(name)
+            f = os.path.abspath(getattr(mod, "__file__", "") or "")
+            out[name] = "stand-in" if f.startswith(_STANDINS) else "real " + str(getattr(mod, "__version__", "?"))
+        except ImportError:
+            out[name] = "missing"
+    return out
 
 
 def import_reference():

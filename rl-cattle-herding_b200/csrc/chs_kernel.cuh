@@ -395,6 +395,24 @@ __global__ void __launch_bounds__(256) alpha_mask_kernel(const typename VT<T>::v
     out[(size_t)idx * nch + c] = alpha_chunk_mask<T>([&](int j) { return r[j]; }, qi, i, c * 32, M);
 }
 
+// After a state injection: do the herd positions of every env still equal its spawn row bit for bit?  (Then the
+// alpha-range table stays valid.)  One thread per (cow, env); *bad counts the mismatches.
+template <typename T>
+__global__ void __launch_bounds__(256) spawn_row_check_kernel(const KArgs<T> a, int* bad) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const KParams& p = a.p;
+  if (idx >= (long long)p.M * p.E) return;
+  const int j = (int)(idx / p.E), e = (int)(idx - (long long)j * p.E);
+  const int row = a.envi[e].w;
+  bool ok = row >= 0 && row < p.n_sims;
+  if (ok) {
+    const auto c = a.cpos[idx];
+    const auto r = a.spawn[(size_t)row * p.spawn_stride + j];
+    ok = (c.x == r.x) && (c.y == r.y);
+  }
+  if (!ok) atomicAdd(bad, 1);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
   const KParams& p = a.p;

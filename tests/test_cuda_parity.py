@@ -44,12 +44,18 @@ def _mask_near_ties(g, obs, ref_obs, tol=2e-5):
     return obs
 
 
-def _env_for(g, precision, extra=0):
+def _env_for(g, precision, extra=0, mode="auto", variant=0):
+    """`mode`: chs_set_step_mode (fused = one kernel, split = drone_kernel + step_kernel<SPLIT>); `variant`: register
+    budget of the fp32 step kernel (1 = 128 registers, 2 = the 64-register build every large batch runs)."""
     import rl_cattle_herding_b200 as pkg
     m = g.meta
     env = pkg.CattleHerdingBatchedEnv(g.steps + extra, num_drones=12, num_cattle=m["n_cattle"], ctrl_freq=m["ctrl_freq"],
                                       pyb_freq=m["pyb_freq"], act=m["act"], start_level=m["start_level"],
-                                      auto_reset=False, precision=precision, spawn_table=g.table, device=0)
+                                      auto_reset=False, precision=precision, spawn_table=g.table, device=0, step_mode=mode)
+    if variant:
+        if variant == 2:
+            env.set_launch(16, 256)          # the CTA shape large batches use with this build
+        pkg._lib.check(env.lib.chs_set_register_variant(env._h, variant))
     return env
 
 
@@ -58,11 +64,17 @@ def _inject(env, g, which="before"):
     env.set_state(st)
 
 
-@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+# every build of the step that ships: the fp64 instrument and both register budgets of the fp32 product, each as one
+# fused kernel and as the split pair, all against the same recordings of the reference
+BUILDS = [("fp64", "fused", 0), ("fp64", "split", 0), ("fp32", "fused", 1), ("fp32", "split", 1), ("fp32", "fused", 2),
+          ("fp32", "split", 2)]
+
+
+@pytest.mark.parametrize("precision,mode,variant", BUILDS, ids=lambda b: str(b))
 @pytest.mark.parametrize("name", golden_names())
-def test_teacher_forced(name, precision):
+def test_teacher_forced(name, precision, mode, variant):
     g = Golden(name)
-    env = _env_for(g, precision)
+    env = _env_for(g, precision, mode=mode, variant=variant)
     nb, herd = env.enable_debug_outputs()
     _inject(env, g)
     acts = torch.from_numpy(np.ascontiguousarray(g.z["action"])).cuda()
