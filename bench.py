@@ -114,25 +114,32 @@ class ClockSampler:
 
 
 # ======================================================================================================
-# CPU arm: the float64 numpy/python port of the reference algorithm (oracle/cattle_oracle.py), which is
-# pinned to the reference's own outputs by tests/test_oracle_golden.py.  The reference itself is Python and
-# needs /root/reference + pybullet, neither of which exists on the GPU box.
+# CPU arm.  `oracle/ref_arm.py` times the reference's OWN code (the unmodified package from /root/reference, or its
+# byte-for-byte staged copy oracle/_ref on the GPU box; pybullet is a stand-in) single-process and in
+# a SubprocVecEnv-shaped pool; the float64 port (oracle/cattle_oracle.py) is timed beside it.  Checker / baseline use
+# of oracle/ only: nothing below is on the product path.
 # ======================================================================================================
-def _cpu_worker(args):
-    seed, n, m, ctrl_freq, budget_s, max_steps = args
+def _ref_arm():
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ref_arm
+    return ref_arm
+
+
+def _port_worker(args):
+    seed, n, m, ctrl_freq, budget_s = args
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import cattle_oracle as co
     import importlib.util
     spec = importlib.util.spec_from_file_location("chs_spawn", os.path.join(ROOT, "rl-cattle-herding_b200", "spawn.py"))
     spawn = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(spawn)
-    table = spawn.generate(16, m, seed=0)
+    table = spawn.generate(16 if m <= 32 else 4, m, seed=0)
     rng = np.random.default_rng(seed)
     env = co.OracleEnv(m, ctrl_freq=ctrl_freq, spawn_table=table, start_level=7)
     env.reset(n, rng.random((m, 2)))
     steps = 0
     t0 = time.perf_counter()
-    while steps < max_steps and time.perf_counter() - t0 < budget_s:
+    while time.perf_counter() - t0 < budget_s:
         a = rng.uniform(-1, 1, (n, 4)).astype(np.float32)
         _, _, term, trunc, _ = env.step(a)
         steps += 1
@@ -141,42 +148,55 @@ def _cpu_worker(args):
     return steps, time.perf_counter() - t0
 
 
-def cpu_env_steps_per_s(n, m, ctrl_freq, budget_s, procs):
-    if procs <= 1:
-        steps, dt = _cpu_worker((1, n, m, ctrl_freq, budget_s, 10 ** 9))
-        return steps / dt, 1, f"1 env, {steps} control steps ({dt:.1f} s), resets as they occur"
-    import multiprocessing as mp
-    with mp.get_context("fork").Pool(procs) as pool:
-        t0 = time.perf_counter()
-        res = pool.map(_cpu_worker, [(100 + i, n, m, ctrl_freq, budget_s, 10 ** 9) for i in range(procs)])
-        wall = time.perf_counter() - t0
-    steps = sum(r[0] for r in res)
-    return steps / wall, procs, f"{procs} processes x 1 env, {steps} control steps in {wall:.1f} s wall, resets as they occur"
+def port_env_steps_per_s(n, m, ctrl_freq, budget_s):
+    steps, dt = _port_worker((1, n, m, ctrl_freq, budget_s))
+    return steps / dt
+
+
+def cpu_baseline_single(n, m, ctrl_freq, budget_s):
+    """The `cpu_baseline` object of the GPU line: the reference, one process, on this box's host."""
+    ra = _ref_arm()
+    v, sample = ra.time_single(n, m, ctrl_freq, budget_s)
+    out = {"value": v, "unit": "env-steps/s", "cores": 1, "kind": ra.kind(), "sample": sample}
+    out.update(ra.host_info())
+    out["third_party"] = ra.third_party()
+    out["port"] = {"value": port_env_steps_per_s(n, m, ctrl_freq, min(4.0, budget_s)), "unit": "env-steps/s", "cores": 1,
+                   "what": "oracle/cattle_oracle.py (float64 restatement), same workload"}
+    return out
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
-    try:
-        cores = len(os.sched_getaffinity(0))
-    except AttributeError:
-        pass
+    ra = _ref_arm()
+    host = ra.host_info()
+    cores = host["cores_visible"]
     K, W = max(1, args.steps), args.warmup
-    # each "step" of this arm is a bounded sample: every process advances its env for a slice of the budget
-    budget = max(2.0, min(args.cpu_seconds * 4, 60.0))
-    value, used, sample = cpu_env_steps_per_s(args.drones, args.cattle, args.ctrl_freq, budget, cores)
+    b = max(3.0, min(args.cpu_seconds, 20.0))
+    n, m = args.drones, args.cattle
+    single, single_s = ra.time_single(n, m, args.ctrl_freq, b)
+    pool, used, pool_s = ra.time_pool(n, m, args.ctrl_freq, b * 1.5, cores)
+    c3_single, c3_single_s = ra.time_single(8, 100, args.ctrl_freq, b)
+    c3_pool, _, c3_pool_s = ra.time_pool(8, 100, args.ctrl_freq, b * 1.5, cores)
+    port = port_env_steps_per_s(n, m, args.ctrl_freq, 4.0)
     line = {
-        "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
-        "ms_per_step": 1000.0 / value, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": "env-steps/sec", "value": pool, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
+        "ms_per_step": 1000.0 / pool, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "impl": "reference",
-        "config": {"workload": f"{args.drones} drones / {args.cattle} cattle, Physics.DYN, VEL actions, 240 Hz / "
-                               f"{args.ctrl_freq} Hz, level 7, uniform random actions, auto-reset",
-                   "note": "CPU arm: float64 port of the reference algorithm (oracle/cattle_oracle.py, pinned to "
-                           "the reference's outputs); one env per process like SubprocVecEnv, no IPC"},
-        "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": used, "kind": "port", "sample": sample},
-        "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": {"workload": f"CattleAviary Physics.DYN, {n} drones + {m} cattle, VEL actions, 240 Hz physics / "
+                               f"{args.ctrl_freq} Hz ctrl, level 7, uniform random actions, auto-reset",
+                   "note": "CPU arm: the reference's own unmodified Python (gym_pybullet_drones.sb3_envs.CattleAviary) on all "
+                           "host cores, one env per process with one pipe round trip per step (SubprocVecEnv protocol, "
+                           "simulator/CTDECattleHerder.py:91-97); pybullet is the stand-in body store of "
+                           "oracle/ref_harness/standins (the real package is installed on neither box)"},
+        "cpu_baseline": {"value": pool, "unit": "env-steps/s", "cores": used, "kind": ra.kind(), "sample": pool_s,
+                         "single_process": {"value": single, "sample": single_s},
+                         "c3_8d100c": {"single_process": {"value": c3_single, "sample": c3_single_s},
+                                       "pool": {"value": c3_pool, "sample": c3_pool_s}},
+                         "port": {"value": port, "cores": 1, "what": "oracle/cattle_oracle.py, single process, same workload"},
+                         "third_party": ra.third_party(), **host},
+        "e2e": {"value": pool, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)

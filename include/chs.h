@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define CHS_ABI_VERSION 2
+#define CHS_ABI_VERSION 3
 #define CHS_MAX_DRONES 12   /* GLOBAL_MAX_NUM_DRONES, BaseAviary.py:112 */
 #define CHS_NUM_STATS 16
 
@@ -88,6 +88,12 @@ typedef struct ChsParams {
   int32_t envs_per_block;     /* launch tuning, 0 = auto */
   int32_t threads_per_block;  /* launch tuning, 0 = auto */
   int32_t reserved0;          /* step mode at creation: 0 auto, 1 fused, 2 split (see chs_set_step_mode) */
+  int32_t persistent_padding; /* 1: rows >= max_drones of every (R, L) observation image are constant zeros OWNED BY THE
+                                 CALLER: chs_reset writes them for the envs it resets, chs_step never touches them (3/4 of
+                                 the bytes of a (12, 66) image at 3 drones).  Buffers handed to chs_step -- obs_dev and
+                                 terminal_obs_dev -- must hold zeros there (zero-fill them once, or chs_reset into them).
+                                 0: every call rewrites the full image (the reference's _computeObs does, BaseRLAviary.py:334) */
+  int32_t reserved1;
   uint64_t seed;              /* Philox key; streams are keyed by (seed, global env id, episode) */
 } ChsParams;
 

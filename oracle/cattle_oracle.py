@@ -155,6 +155,38 @@ def _clip(v, lo, hi):
 # =================================================================================================
 # State container (mirrors ref_harness.capture_state; NMAX drone slots, M cows)
 # =================================================================================================
+def aero_terms(flags, pos, R, vel, rpm, drag_rpm, others, k, n):
+    """The reference's PYB-only aerodynamic models as force terms for drone `k` (sb3_envs/BaseAviary.py:943-1039),
+    pinned to the reference's own outputs by tests/golden/aero/aero_forces.npz (tests/test_oracle_extras.py, 1e-12):
+      ground effect (:943-978)  -> per-propeller extra thrust along body z: kf rpm_i^2 c_g (r_p / 4 h_i)^2, h_i = world
+                                   height of prop i (getLinkStates; cf2x.urdf:42-78) clipped at GND_EFF_H_CLIP; applied
+                                   only if |roll|, |pitch| < pi/2, i.e. R[2][2] = cos(roll) cos(pitch) > 0
+      drag (:982-1009)          -> the reference applies R^T (-(c_xy, c_xy, c_z) * sum(2 pi rpm'/60) * v) in the LINK
+                                   frame of the centre-of-mass link; in world coordinates that is the vector returned
+      downwash (:1013-1039)     -> body-z force: sum over drones i above within 10 m of -a exp(-(dxy/b)^2 / 2),
+                                   a = dw1 (r_p / 4 dz)^2, b = dw2 dz + dw3
+    Returns (gnd[4], drag_world[3], downwash_z)."""
+    gnd = [0.0, 0.0, 0.0, 0.0]
+    if (flags & 2) and R[2][2] > 0:
+        for i, (ox, oy) in enumerate(PROP_XY):
+            h = max(pos[2] + R[2][0] * ox + R[2][1] * oy, GND_EFF_H_CLIP)
+            gnd[i] = rpm[i] * rpm[i] * KF * GND_EFF_COEFF * (PROP_RADIUS / (4 * h)) ** 2
+    drag = [0.0, 0.0, 0.0]
+    if (flags & 1) and drag_rpm is not None:
+        om = (2 * math.pi / 60) * (drag_rpm[0] + drag_rpm[1] + drag_rpm[2] + drag_rpm[3])
+        drag = [-DRAG_XY * om * vel[0], -DRAG_XY * om * vel[1], -DRAG_Z * om * vel[2]]
+    dwz = 0.0
+    if (flags & 4) and others is not None:
+        for i in range(n):
+            dz = others[i][2] - pos[2]
+            dxy = math.sqrt((others[i][0] - pos[0]) ** 2 + (others[i][1] - pos[1]) ** 2)
+            if i != k and dz > 0 and dxy < 10:
+                wgt = math.exp(-0.5 * (dxy / (DW2 * dz + DW3)) ** 2)
+                if wgt > 0:
+                    dwz = dwz - DW1 * (PROP_RADIUS / (4 * dz)) ** 2 * wgt
+    return gnd, drag, dwz
+
+
 STATE_FIELDS = ("n_drones", "pos", "quat", "rpy", "vel", "ang_v", "rpy_rates", "last_rpm",
                 "pid_ipos", "pid_last_rpy", "pid_irpy", "cattle_pos", "cattle_vel", "step_counter",
                 "step_counter_A", "prev_cent_dist", "spacing_clock", "level", "tally", "spawn_idx")
@@ -380,23 +412,11 @@ class OracleEnv:
         pos = self.pos[k]; quat = tuple(self.quat[k]); vel = self.vel[k]; w = self.rpy_rates[k]
         R = quat_to_matrix(quat)
         f = [r * r * KF for r in rpm]
-        if (self.aero_flags & 2) and R[2][2] > 0:
-            for i, (ox, oy) in enumerate(PROP_XY):
-                h = max(pos[2] + R[2][0] * ox + R[2][1] * oy, GND_EFF_H_CLIP)
-                f[i] = f[i] + rpm[i] * rpm[i] * KF * GND_EFF_COEFF * (PROP_RADIUS / (4 * h)) ** 2
-        thrust = f[0] + f[1] + f[2] + f[3]
-        if (self.aero_flags & 4) and pos0 is not None:
-            for i in range(self.n_drones):
-                dz = pos0[i][2] - pos[2]
-                dxy = math.sqrt((pos0[i][0] - pos[0]) ** 2 + (pos0[i][1] - pos[1]) ** 2)
-                if i != k and dz > 0 and dxy < 10:
-                    wgt = math.exp(-0.5 * (dxy / (DW2 * dz + DW3)) ** 2)
-                    if wgt > 0:
-                        thrust = thrust - DW1 * (PROP_RADIUS / (4 * dz)) ** 2 * wgt
-        fw = [R[0][2] * thrust, R[1][2] * thrust, R[2][2] * thrust - GRAVITY]
-        if (self.aero_flags & 1) and drag_rpm is not None:
-            om = (2 * math.pi / 60) * (drag_rpm[0] + drag_rpm[1] + drag_rpm[2] + drag_rpm[3])
-            fw = [fw[0] - DRAG_XY * om * vel[0], fw[1] - DRAG_XY * om * vel[1], fw[2] - DRAG_Z * om * vel[2]]
+        gnd, drag_w, dwz = aero_terms(self.aero_flags, pos, R, vel, rpm, drag_rpm, pos0, k, self.n_drones)
+        for i in range(4):
+            f[i] = f[i] + gnd[i]
+        thrust = f[0] + f[1] + f[2] + f[3] + dwz
+        fw = [R[0][2] * thrust + drag_w[0], R[1][2] * thrust + drag_w[1], R[2][2] * thrust - GRAVITY + drag_w[2]]
         zt = [r * r * KM for r in rpm]
         tz = -zt[0] + zt[1] - zt[2] + zt[3]
         tx = (f[0] + f[1] - f[2] - f[3]) * (ARM / math.sqrt(2))

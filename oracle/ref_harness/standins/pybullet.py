@@ -188,3 +188,41 @@ def getQuaternionFromEuler(e):
             cr * sp * cy + sr * cp * sy,
             cr * cp * sy - sr * sp * cy,
             cr * cp * cy + sr * sp * sy)
+
+
+# ---- external forces (PYB_* physics modes; recorded, never integrated) ---------------------------
+# The reference's aerodynamic models (`sb3_envs/BaseAviary.py:943-1039`) are plain Python up to a final
+# `p.applyExternalForce(...)`.  There is no solver here, so the stand-in RECORDS those calls: the force vectors the
+# reference itself computes for a given state become golden values (tests/golden/aero/aero_forces.npz,
+# oracle/ref_harness/make_aero_golden.py) for the DYN-path restatement of the same models.
+force_log = []
+
+# link frames of assets/cf2x.urdf: links 0-3 are the propellers (inertial origins at :42,54,66,78, fixed joints without
+# an origin), link 4 is `center_of_mass_link` at the base origin (:86-95)
+_CF2X_LINK_XYZ = ((0.028, -0.028, 0.0), (-0.028, -0.028, 0.0), (-0.028, 0.028, 0.0), (0.028, 0.028, 0.0), (0.0, 0.0, 0.0))
+
+
+def applyExternalForce(objectUniqueId, linkIndex, forceObj, posObj, flags, physicsClientId=0):
+    force_log.append({"kind": "force", "body": int(objectUniqueId), "link": int(linkIndex),
+                      "force": tuple(float(v) for v in forceObj), "pos": tuple(float(v) for v in posObj),
+                      "flags": int(flags)})
+
+
+def applyExternalTorque(objectUniqueId, linkIndex, torqueObj, flags, physicsClientId=0):
+    force_log.append({"kind": "torque", "body": int(objectUniqueId), "link": int(linkIndex),
+                      "torque": tuple(float(v) for v in torqueObj), "flags": int(flags)})
+
+
+def getLinkStates(bodyUniqueId, linkIndices, computeLinkVelocity=0, computeForwardKinematics=0, physicsClientId=0):
+    """linkWorldPosition of each requested link (centre of mass of the link: base position + R(base quat) . inertial
+    origin); the remaining entries of a link state are not used by the reference and are returned as zeros."""
+    b = _world(physicsClientId)["bodies"][bodyUniqueId]
+    R = getMatrixFromQuaternion(b.quat)
+    out = []
+    for li in linkIndices:
+        ox, oy, oz = _CF2X_LINK_XYZ[li]
+        wp = (b.pos[0] + R[0] * ox + R[1] * oy + R[2] * oz,
+              b.pos[1] + R[3] * ox + R[4] * oy + R[5] * oz,
+              b.pos[2] + R[6] * ox + R[7] * oy + R[8] * oz)
+        out.append((wp, b.quat, (0.0, 0.0, 0.0), (0.0, 0.0, 0.0, 1.0), wp, b.quat, (0.0, 0.0, 0.0), (0.0, 0.0, 0.0)))
+    return out

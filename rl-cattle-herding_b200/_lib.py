@@ -8,7 +8,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("CHS_LIB", os.path.join(_HERE, "libchs.so"))   # CHS_LIB: build-variant experiments
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 MAX_DRONES = 12
 NUM_STATS = 16
 
@@ -28,7 +28,7 @@ class ChsParams(C.Structure):
                 ("packing", C.c_int32), ("precision", C.c_int32), ("auto_reset", C.c_int32),
                 ("aero_flags", C.c_int32), ("cattle_integrate", C.c_int32), ("env_id_offset", C.c_int32),
                 ("envs_per_block", C.c_int32), ("threads_per_block", C.c_int32), ("step_mode", C.c_int32),
-                ("seed", C.c_uint64)]
+                ("persistent_padding", C.c_int32), ("reserved1", C.c_int32), ("seed", C.c_uint64)]
 
 
 class ChsDims(C.Structure):

@@ -37,12 +37,18 @@ class CattleHerdingBatchedEnv:
     `packing="marl"` selects the rllib_envs semantics (MARLCattleAviary / BaseMARLAviary): per-drone
     observation rows without the 12-slot neighbour gap, `reward` (E, D), `terminated` / `truncated` (E, D+1)
     whose last column is RLlib's "__all__" entry; `auto_reset` fires on either "__all__" flag.
+
+    `persistent_padding` (default on): rows >= num_drones of the (12, L) observation images are constant zeros
+    (`BaseRLAviary._computeObs` pads every observation to GLOBAL_MAX_NUM_DRONES rows, BaseRLAviary.py:334).  The
+    tensors `self.obs` / `self.terminal_obs` (and the pinned host mirrors) are owned by this object and are created
+    zero-filled, so the simulator writes those rows at `reset()` only and never again: 3/4 of the bytes of an image
+    at 3 drones.  Turn it off to have every step rewrite the full image.
     """
 
     def __init__(self, num_envs, num_drones=3, num_cattle=20, pyb_freq=240, ctrl_freq=30, act="vel",
                  start_level=7, fixed_num_drones=0, obs_rows=None, auto_reset=True, precision="fp32",
                  spawn_table=None, device=None, env_id_offset=0, seed=0, envs_per_block=0, threads_per_block=0,
-                 packing="ctde", aero=0, cattle_integrate=False, step_mode="auto"):
+                 packing="ctde", aero=0, cattle_integrate=False, step_mode="auto", persistent_padding=True):
         if not torch.cuda.is_available():
             raise RuntimeError("CattleHerdingBatchedEnv needs a CUDA device (there is no CPU fallback)")
         self.lib = _lib.load()
@@ -64,6 +70,8 @@ class CattleHerdingBatchedEnv:
         p.obs_rows, p.packing, p.precision = int(obs_rows), {"ctde": 0, "marl": 1}[packing], {"fp32": 0, "fp64": 1}[precision]
         p.auto_reset, p.env_id_offset, p.seed = int(bool(auto_reset)), int(env_id_offset), int(seed)
         p.envs_per_block, p.threads_per_block = int(envs_per_block), int(threads_per_block)
+        p.persistent_padding = int(bool(persistent_padding))
+        self.persistent_padding = bool(persistent_padding)
         self._h = C.c_void_p(0)
         _lib.check(self.lib.chs_create(C.byref(p), int(num_envs), self.device.index, C.byref(self._h)))
         d = _lib.ChsDims()
@@ -177,12 +185,21 @@ class CattleHerdingBatchedEnv:
                                            C.c_void_p(self._host["obs"].data_ptr()), self._stream()))
         return hb["obs"]
 
-    def step_host(self, actions):
+    @property
+    def host_actions(self):
+        """The pinned (E, D, A) float32 action buffer of the host path.  Fill it in place and call
+        `step_host()` without an argument (or with this very array) to skip the copy of the actions."""
+        return self._host_buffers()["actions"]
+
+    def step_host(self, actions=None):
         """numpy actions (E, D, A) -> numpy (obs, reward, terminated, truncated, done_idx, terminal_obs[:n]).
-        All copies (pinned host <-> device) happen inside the C call; arrays are views of pinned buffers that
-        are overwritten by the next call."""
+        The returned arrays are views of PINNED buffers owned by this object, overwritten by the next call.  The
+        kernel reads the actions from, and writes the observations and terminal observations straight into, those
+        pinned buffers over PCIe (no staging in HBM, no separate copy); reward / flags / done indices come back in one
+        small copy.  `actions=None` (or the `host_actions` array itself): the pinned action buffer was filled in place."""
         hb = self._host_buffers()
-        np.copyto(hb["actions"], np.asarray(actions, dtype=np.float32).reshape(hb["actions"].shape))
+        if actions is not None and actions is not hb["actions"]:
+            np.copyto(hb["actions"], np.asarray(actions, dtype=np.float32).reshape(hb["actions"].shape))
         h = self._host
         _lib.check(self.lib.chs_step_host(self._h, _ptr(h["actions"]), _ptr(h["obs"]), _ptr(h["reward"]),
                                           _ptr(h["terminated"]), _ptr(h["truncated"]), C.byref(self._n_done),

@@ -15,6 +15,17 @@ using namespace chs;
 
 static thread_local char g_err[512] = "";
 
+// NVTX ranges around the entry points: nvtx3 is header-only and resolves the injection library at
+// run time, so without a profiler attached these are a pointer test.
+#if __has_include(<nvtx3/nvToolsExt.h>)
+#include <nvtx3/nvToolsExt.h>
+static inline void nvtx_push(const char* name) { nvtxRangePushA(name); }
+static inline void nvtx_pop() { nvtxRangePop(); }
+#else
+static inline void nvtx_push(const char*) {}
+static inline void nvtx_pop() {}
+#endif
+
 static int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -52,8 +63,9 @@ struct ChsHandle {
   // CHS_FULL_KERNEL=1 never use the lean build, CHS_INLINE_RESET=1 reset inside step_kernel in split mode too
   unsigned char* d_small;           // host path: count | reward | flags | done idx in one block (chs_api_io.inc)
   unsigned char* h_small;           // pinned mirror
-  const void* zeroed_obs_host;      // host buffers whose padding rows have been zero-filled (chs_api_io.inc)
-  const void* zeroed_termobs_host;
+  struct { const void* ptr; size_t bytes; } zeroed_host[4];   // pageable host buffers whose padding rows were zero-filled (chs_api_io.inc)
+  unsigned zeroed_next;
+  bool knob_no_direct;              // CHS_NO_DIRECT=1: the host path stages through HBM even for pinned buffers
   int knob_smem_pad;
   bool knob_full, knob_inline_reset;
   int *dbg_nb, *dbg_herd;
@@ -67,7 +79,6 @@ struct ChsHandle {
   float *d_actions, *d_obs, *d_reward, *d_termobs;
   uint8_t *d_term, *d_trunc, *d_mask;
   int *d_count, *d_idx;
-  int* h_count;               // pinned
 };
 
 struct DeviceGuard {
@@ -191,15 +202,18 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   if ((kp.stage_stride & 31) == 0) kp.stage_stride += 4;
   kp.vec4_ok = ((kp.R * kp.L) % 4 == 0) ? 1 : 0;
   kp.bulk_ok = (kp.vec4_ok && !getenv("CHS_NO_BULK")) ? 1 : 0;
+  // persistent padding needs real padding rows and float4-addressable images (the reset kernel zero-fills them)
+  kp.pad_persist = (prm->persistent_padding && R > prm->max_drones && kp.vec4_ok) ? 1 : 0;
   {
     const int total = kp.R * kp.L * 4, c1 = kp.stage_stride * 4 < total ? kp.stage_stride * 4 : total;
-    kp.zero_bytes = kp.bulk_ok ? total - c1 : 0;
+    kp.zero_bytes = (kp.bulk_ok && !kp.pad_persist) ? total - c1 : 0;
   }
   h->step_mode = prm->reserved0;
   { const char* v = getenv("CHS_SMEM_PAD"); h->knob_smem_pad = v ? atoi(v) : 0; }
   h->knob_full = getenv("CHS_FULL_KERNEL") != nullptr;
   kp.early_ok = getenv("CHS_NO_EARLY") ? 0 : 1;
   h->knob_inline_reset = getenv("CHS_INLINE_RESET") != nullptr;
+  h->knob_no_direct = getenv("CHS_NO_DIRECT") != nullptr;
   kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
   kp.aero_flags = prm->aero_flags;
@@ -220,7 +234,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   ALLOC0(h->epret, E * sizeof(double));
   ALLOC0(h->envi, E * sizeof(int4));
   ALLOC0(h->envj, E * sizeof(int4));
-  ALLOC0(h->stats, CHS_NUM_STATS * sizeof(double));
+  ALLOC0(h->stats, (size_t)CHS_STAT_ROWS * CHS_NUM_STATS * sizeof(double));
   ALLOC0(h->tab, 152 * sizeof(double));
   ALLOC0(h->own2, D * E * 4 * ts);
   ALLOC0(h->done_list, E * sizeof(int));
@@ -386,8 +400,11 @@ extern "C" int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_d
   if (!h->spawn_set) return fail(CHS_ERR_STATE, "chs_set_spawn_table must be called before chs_reset");
   if (obs_dev && h->kp.vec4_ok && !aligned16(obs_dev)) return fail(CHS_ERR_INVALID, "obs_dev must be 16-byte aligned");
   DeviceGuard dg(h->device);
-  return h->f64 ? launch_reset<double>(h, env_mask_dev, obs_dev, (cudaStream_t)stream)
-                : launch_reset<float>(h, env_mask_dev, obs_dev, (cudaStream_t)stream);
+  nvtx_push("chs_reset");
+  const int rc = h->f64 ? launch_reset<double>(h, env_mask_dev, obs_dev, (cudaStream_t)stream)
+                        : launch_reset<float>(h, env_mask_dev, obs_dev, (cudaStream_t)stream);
+  nvtx_pop();
+  return rc;
 }
 
 template <typename T> static void launch_step_variant(ChsHandle* h, const KArgs<T>& a, int grid, cudaStream_t st);
@@ -451,10 +468,13 @@ extern "C" int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, 
   if (h->kp.vec4_ok && ((obs_dev && !aligned16(obs_dev)) || (terminal_obs_dev && !aligned16(terminal_obs_dev))))
     return fail(CHS_ERR_INVALID, "obs buffers must be 16-byte aligned");
   DeviceGuard dg(h->device);
-  return h->f64 ? launch_step<double>(h, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
-                                      terminal_obs_dev, 1, nullptr, nullptr, (cudaStream_t)stream)
-                : launch_step<float>(h, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
-                                     terminal_obs_dev, 1, nullptr, nullptr, (cudaStream_t)stream);
+  nvtx_push("chs_step");
+  const int rc = h->f64 ? launch_step<double>(h, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
+                                              terminal_obs_dev, 1, nullptr, nullptr, (cudaStream_t)stream)
+                        : launch_step<float>(h, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
+                                             terminal_obs_dev, 1, nullptr, nullptr, (cudaStream_t)stream);
+  nvtx_pop();
+  return rc;
 }
 
 #include "chs_api_io.inc"

@@ -160,48 +160,66 @@ __device__ __forceinline__ void action_to_rpm(const KParams& p, DroneState<T>& s
 }
 
 // K substeps of BaseAviary._dynamics (:1043-1102) + _integrateQ (:1104-1117) with constant rpm.
+// The loop is the longest dependent chain of the whole step (K = 8 at 240/30 Hz), so it carries only what the next
+// substep needs:
+//   * the stored quaternion is unit (Bullet hands back a normalised one, BaseAviary.py:713), so getMatrixFromQuaternion's
+//     s = 2/|q|^2 is 2 up to the rounding of that normalisation, and of the rotation matrix only the body z axis (thrust
+//     direction) is used inside the loop; the full matrix is built once, after the loop, from the quaternion that entered
+//     the last substep (ang_v = R_prev . rpy_rates, :1096-1100);
+//   * the body rates do not depend on the attitude (torques are constant over the control step), so their chain runs
+//     beside the quaternion chain; _integrateQ's isclose(|w|, 0) early-out (:1106) is a select, not a branch;
+//   * the renormalisation 1/sqrt(n2) of a quaternion that one exact rotation step has moved off the unit sphere by
+//     rounding only (n2 = 1 + O(1e-7)) is 1.5 - 0.5 n2 to O(1e-14) in the float build.
 template <typename T>
 __device__ __forceinline__ void dyn_substeps(DroneState<T>& s, const T rpm[4], int K, T dt) {
   // forces and body torques are constant over the K substeps (rpm is)
   T f[4], zt[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) { const T r2 = rpm[i] * rpm[i]; f[i] = r2 * T(k::KF); zt[i] = r2 * T(k::KM); }
-  const T thrust = f[0] + f[1] + f[2] + f[3];
+  const T acc = (f[0] + f[1] + f[2] + f[3]) * T(1.0 / k::M_KG);      // thrust / m
   const T tz = -zt[0] + zt[1] - zt[2] + zt[3];
   // the sign of tx is the reference's (positive feedback on roll) -- do not "fix"
   const T tx = (f[0] + f[1] - f[2] - f[3]) * T(k::ARM / k::SQRT2);
   const T ty = (-f[0] + f[1] + f[2] - f[3]) * T(k::ARM / k::SQRT2);
-  T R[3][3];
+  T x = s.q[0], y = s.q[1], z = s.q[2], ww = s.q[3];
+  T px = x, py = y, pz = z, pw = ww;          // quaternion entering the last substep
+  const T hdt = dt * T(0.5);
+#pragma unroll 1
   for (int it = 0; it < K; ++it) {
-    quat_to_matrix<T>(s.q, R);
-    const T fw[3] = {R[0][2] * thrust, R[1][2] * thrust, R[2][2] * thrust - T(k::GRAVITY)};
+    px = x; py = y; pz = z; pw = ww;
+    // body z axis in world coordinates (third column of getMatrixFromQuaternion)
+    const T zx = T(2) * (x * z + ww * y), zy = T(2) * (y * z - ww * x), zz = T(1) - T(2) * (x * x + y * y);
     const T Jw[3] = {T(k::IXX) * s.w[0], T(k::IYY) * s.w[1], T(k::IZZ) * s.w[2]};
     const T cr[3] = {s.w[1] * Jw[2] - s.w[2] * Jw[1], s.w[2] * Jw[0] - s.w[0] * Jw[2], s.w[0] * Jw[1] - s.w[1] * Jw[0]};
-    const T wd[3] = {(tx - cr[0]) * T(1.0 / k::IXX), (ty - cr[1]) * T(1.0 / k::IYY), (tz - cr[2]) * T(1.0 / k::IZZ)};
-#pragma unroll
-    for (int i = 0; i < 3; ++i) s.v[i] = s.v[i] + dt * (fw[i] * T(1.0 / k::M_KG));
-#pragma unroll
-    for (int i = 0; i < 3; ++i) s.w[i] = s.w[i] + dt * wd[i];
+    s.v[0] = s.v[0] + dt * (zx * acc);
+    s.v[1] = s.v[1] + dt * (zy * acc);
+    s.v[2] = s.v[2] + dt * (zz * acc - T(k::GRAVITY / k::M_KG));
+    s.w[0] = s.w[0] + dt * ((tx - cr[0]) * T(1.0 / k::IXX));
+    s.w[1] = s.w[1] + dt * ((ty - cr[1]) * T(1.0 / k::IYY));
+    s.w[2] = s.w[2] + dt * ((tz - cr[2]) * T(1.0 / k::IZZ));
 #pragma unroll
     for (int i = 0; i < 3; ++i) s.p[i] = s.p[i] + dt * s.v[i];
-    const T wn = Mth<T>::sqrt(s.w[0] * s.w[0] + s.w[1] * s.w[1] + s.w[2] * s.w[2]);
-    T x = s.q[0], y = s.q[1], z = s.q[2], ww = s.q[3];
-    if (!(wn <= T(1e-8))) {      // np.isclose(norm, 0): atol 1e-8
-      const T pp = s.w[0], qq = s.w[1], rr = s.w[2];
-      T sn, c;
-      Mth<T>::sincos_small(wn * dt * T(0.5), &sn, &c);
-      const T sc = sn * Mth<T>::frcp(wn);        // (2/|w|) * (1/2) * sin(theta)
-      const T nx = c * x + sc * (rr * y - qq * z + pp * ww);
-      const T ny = c * y + sc * (-rr * x + pp * z + qq * ww);
-      const T nz = c * z + sc * (qq * x - pp * y + rr * ww);
-      const T nw = c * ww + sc * (-pp * x - qq * y - rr * z);
-      x = nx; y = ny; z = nz; ww = nw;
-    }
-    const T in = Mth<T>::rsqrt(x * x + y * y + z * z + ww * ww);   // Bullet returns a unit quaternion
-    s.q[0] = x * in; s.q[1] = y * in; s.q[2] = z * in; s.q[3] = ww * in;
+    const T pp = s.w[0], qq = s.w[1], rr = s.w[2];
+    const T wn2 = pp * pp + qq * qq + rr * rr;
+    const bool moving = !(wn2 <= T(1e-16));            // np.isclose(norm, 0): atol 1e-8 (NaN takes the update, like numpy)
+    const T iw = Mth<T>::rsqrt(wn2);
+    T sn, c;
+    Mth<T>::sincos_small(moving ? (wn2 * iw) * hdt : T(0), &sn, &c);     // |w| = 0: 0 * inf stays out of sincos
+    const T sc = moving ? sn * iw : T(0);               // (2/|w|) * (1/2) * sin(theta)
+    c = moving ? c : T(1);
+    const T nx = c * x + sc * (rr * y - qq * z + pp * ww);
+    const T ny = c * y + sc * (-rr * x + pp * z + qq * ww);
+    const T nz = c * z + sc * (qq * x - pp * y + rr * ww);
+    const T nw = c * ww + sc * (-pp * x - qq * y - rr * z);
+    const T in = Mth<T>::rsqrt_near_one(nx * nx + ny * ny + nz * nz + nw * nw);   // Bullet returns a unit quaternion
+    x = nx * in; y = ny * in; z = nz * in; ww = nw * in;
   }
+  s.q[0] = x; s.q[1] = y; s.q[2] = z; s.q[3] = ww;
   // ang_v = R_prev . rpy_rates of the LAST substep (:1096-1100); earlier ones are overwritten
   if (K > 0) {
+    const T pq[4] = {px, py, pz, pw};
+    T R[3][3];
+    quat_to_matrix<T>(pq, R);
 #pragma unroll
     for (int i = 0; i < 3; ++i) s.av[i] = R[i][0] * s.w[0] + R[i][1] * s.w[1] + R[i][2] * s.w[2];
   }

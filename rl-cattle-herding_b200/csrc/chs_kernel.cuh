@@ -81,7 +81,7 @@ __device__ __forceinline__ void bulk_copy_rows(const KParams& p, const float* st
   unsigned c1 = (unsigned)p.stage_stride * 4u;
   if (c1 > total) c1 = total;
   bulk_store(dst, stage_g, c1);
-  if (total > c1) bulk_store(reinterpret_cast<char*>(dst) + c1, zeros, total - c1);
+  if (total > c1 && !p.pad_persist) bulk_store(reinterpret_cast<char*>(dst) + c1, zeros, total - c1);
 }
 
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
@@ -104,11 +104,14 @@ __device__ __forceinline__ void copy_rows(const KParams& p, const float* stage_g
     }
     if (r < sq) { __stcs(dst4 + r, src4[r]); r += 32; }
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!p.pad_persist) {
 #pragma unroll 4
-    for (; r < nq; r += 32) __stcs(dst4 + r, z);
+      for (; r < nq; r += 32) __stcs(dst4 + r, z);
+    }
   } else {
     const int DL = p.D * p.L;
-    for (int r = lane; r < RL; r += 32) __stcs(dst + r, r < DL ? stage_g[r] : 0.f);
+    const int end = p.pad_persist ? (DL < RL ? DL : RL) : RL;
+    for (int r = lane; r < end; r += 32) __stcs(dst + r, r < DL ? stage_g[r] : 0.f);
   }
 }
 
@@ -191,6 +194,14 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
       bulk_copy_rows(p, s.stage + (size_t)g * p.stage_stride, s.zeros, a.obs + (size_t)(e0 + g) * p.R * p.L);
       bulk_commit();
       bulk_wait_read();
+    }
+    if (p.pad_persist) {
+      // chs_reset is the one call that writes the caller-owned padding rows (ChsParams.persistent_padding)
+      const int q0 = p.stage_stride >> 2, nq = (p.R * p.L) >> 2;
+      for (int it = t; it < nd * (nq - q0); it += nt) {
+        const int g = s.dlist[it / (nq - q0)];
+        reinterpret_cast<float4*>(a.obs + (size_t)(e0 + g) * p.R * p.L)[q0 + it % (nq - q0)] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
     }
   } else if (FULL && a.obs) {
     const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
@@ -373,7 +384,10 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
     for (int c = cbase + 32 + lane; c < L; c += 32) orow[c] = 0.f;
   }
   const int zfrom = (n < p.R ? n : p.R) * L;
-  if (p.vec4_ok) {       // R*L is a multiple of 4 and the image is 16-byte aligned: the zero rows go out as float4
+  if (p.pad_persist) {   // rows >= D are the caller's constant zeros; only unused drone slots (n < D) are cleared
+    const int zend = (D < p.R ? D : p.R) * L;
+    for (int idx = zfrom + lane; idx < zend; idx += 32) ob[idx] = 0.f;
+  } else if (p.vec4_ok) {       // R*L is a multiple of 4 and the image is 16-byte aligned: the zero rows go out as float4
     const int z4 = (zfrom + 3) >> 2;
     if (zfrom + lane < (z4 << 2)) ob[zfrom + lane] = 0.f;        // up to 3 floats to the next 16-byte boundary
     float4* o4 = reinterpret_cast<float4*>(ob);
@@ -628,7 +642,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   const bool obs_lane = (!FULL || p.bulk_ok) && a.obs != nullptr && ow >= 0 && ow < G && e0 + ow < E;
   if (obs_lane) {
     const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_stride * 4u;
-    if (total > c1) {
+    if (total > c1 && !p.pad_persist) {
       fence_async_smem();
       bulk_store(reinterpret_cast<char*>(a.obs + (size_t)(e0 + ow) * p.R * p.L) + c1, s.zeros, total - c1);
       bulk_commit();
@@ -986,31 +1000,22 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       st_bad = !(r_global == r_global) || fabs(r_global) == Mth<double>::inf();
       done_env = fin && p.auto_reset;          // the observation of this step goes to term_obs, a fresh one to obs
     }
-    // ---- warp-converged: episode statistics and list slots with ONE atomic per counter per warp.  Thousands of
-    // finished envs per step hitting the same few addresses with one atomic each serialise in L2. ----
+    // ---- episode statistics: fire-and-forget reductions (RED, no return value, nothing waits on them) into the row of the
+    // [CHS_STAT_ROWS][CHS_NUM_STATS] accumulator picked by the CTA index, so that the thousands of envs that finish in one
+    // step of a large batch do not queue on sixteen addresses; chs_stats sums the rows.
+    if (active) {
+      double* srow = a.stats + (size_t)(blockIdx.x & (CHS_STAT_ROWS - 1)) * CHS_NUM_STATS;
+      if (st_bad) atomicAdd(srow + 9, 1.0);
+      if (fin) {
+        atomicAdd(srow + 0, 1.0);
+        atomicAdd(srow + 1, epret);
+        atomicAdd(srow + 2, (double)scA);
+        if (st_term) atomicAdd(srow + 3, 1.0);
+        if (st_trunc && st_cause >= 0) atomicAdd(srow + 4 + st_cause, 1.0);
+      }
+    }
     {
       const unsigned full = 0xffffffffu, lt = (1u << t) - 1u;
-      const unsigned fm = __ballot_sync(full, fin);
-      const unsigned bm = __ballot_sync(full, st_bad);
-      if (bm && t == 0) atomicAdd(a.stats + 9, (double)__popc(bm));
-      if (fm) {
-        double ret = fin ? epret : 0.0;
-        int len = fin ? scA : 0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { ret += __shfl_xor_sync(full, ret, o); len += __shfl_xor_sync(full, len, o); }
-        const unsigned tm = __ballot_sync(full, fin && st_term);
-        unsigned cm[5];
-#pragma unroll
-        for (int c = 0; c < 5; ++c) cm[c] = __ballot_sync(full, fin && st_trunc && st_cause == c);
-        if (t == 0) {
-          atomicAdd(a.stats + 0, (double)__popc(fm));
-          atomicAdd(a.stats + 1, ret);
-          atomicAdd(a.stats + 2, (double)len);
-          if (tm) atomicAdd(a.stats + 3, (double)__popc(tm));
-#pragma unroll
-          for (int c = 0; c < 5; ++c) if (cm[c]) atomicAdd(a.stats + 4 + c, (double)__popc(cm[c]));
-        }
-      }
       const unsigned dm = __ballot_sync(full, done_env);
       if (dm) {
         const int lead = __ffs(dm) - 1, cnt = __popc(dm), off = __popc(dm & lt);

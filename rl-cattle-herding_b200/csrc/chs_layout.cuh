@@ -21,6 +21,8 @@
 
 namespace chs {
 
+constexpr int CHS_STAT_ROWS = 1024;   // rows of the statistics accumulator (a power of two); chs_stats sums them
+
 enum DroneField { F_A = 0, F_B, F_C, F_D, F_E, F_F, F_G, F_COUNT };
 
 struct KParams {
@@ -41,6 +43,7 @@ struct KParams {
   int split;             // 1: drones are integrated by drone_kernel, step_kernel does the rest
   int bulk_ok;           // observations leave through bulk (TMA) stores: R*L*4 and the staging stride are multiples of 16 B
   int zero_bytes;        // size of the shared zero block = R*L*4 - min(stage_stride*4, R*L*4)
+  int pad_persist;       // rows >= D of an obs image are caller-owned zeros: chs_step does not write them (ChsParams.persistent_padding)
   int early_ok;          // warp 0 may start its drone chain before the other warps finish staging (CHS_NO_EARLY=1 clears it)
   uint32_t seed_lo, seed_hi;
 };
@@ -59,7 +62,7 @@ template <typename T> struct KArgs {
   double* epret;
   const typename VT<T>::v2* spawn;   // [n_sims][spawn_stride]
   const unsigned* amask;             // nullable [n_sims][M][ceil(M/32)]: alpha-term in-range masks per spawn row (chs_flock.cuh)
-  double* stats;                     // [CHS_NUM_STATS]
+  double* stats;                     // [CHS_STAT_ROWS][CHS_NUM_STATS], row = CTA index mod CHS_STAT_ROWS
   const double* tab;                 // [CHS_TAB_DOUBLES] curriculum rows + 1/n (chs_task.cuh)
   // per-call
   const float* actions;              // [E][D][A]

@@ -26,6 +26,11 @@ template <> struct Mth<float> {
   static __device__ __forceinline__ float rcp(float x) { return __frcp_rn(x); }
   // 1-2 ulp approximations on the MUFU pipe; the fp32 parity budget is 1e-5 relative
   static __device__ __forceinline__ float rsqrt(float x) { return rsqrtf(x); }
+  // 1/sqrt(x) for x = 1 + O(1e-7) (renormalisation of a quaternion that left the unit sphere by rounding only): the first
+  // order expansion is exact to O((x-1)^2) and keeps the MUFU latency off the substep chain; anything else takes MUFU.RSQ
+  static __device__ __forceinline__ float rsqrt_near_one(float x) {
+    return (fabsf(x - 1.0f) < 1e-3f) ? fmaf(-0.5f, x, 1.5f) : rsqrtf(x);
+  }
   static __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
   static __device__ __forceinline__ float frcp(float x) { return __fdividef(1.0f, x); }
   // cos(pi*x) for x in [0,1] (the bump function's argument): MUFU.COS, abs error ~5e-7
@@ -34,8 +39,9 @@ template <> struct Mth<float> {
   static __device__ __forceinline__ void sincos_small(float x, float* s, float* c) {
     if (fabsf(x) < 0.5f) {
       const float x2 = x * x;
-      *s = x * (1.0f + x2 * (-1.0f / 6.0f + x2 * (1.0f / 120.0f + x2 * (-1.0f / 5040.0f + x2 * (1.0f / 362880.0f)))));
-      *c = 1.0f + x2 * (-0.5f + x2 * (1.0f / 24.0f + x2 * (-1.0f / 720.0f + x2 * (1.0f / 40320.0f + x2 * (-1.0f / 3628800.0f)))));
+      // Taylor to x^7 / x^8: the first dropped terms are x^9/9! < 5.4e-9 and x^10/10! < 2.7e-10 at |x| = 0.5
+      *s = x * (1.0f + x2 * (-1.0f / 6.0f + x2 * (1.0f / 120.0f + x2 * (-1.0f / 5040.0f))));
+      *c = 1.0f + x2 * (-0.5f + x2 * (1.0f / 24.0f + x2 * (-1.0f / 720.0f + x2 * (1.0f / 40320.0f))));
     } else {
       sincosf(x, s, c);
     }
@@ -58,6 +64,7 @@ template <> struct Mth<double> {
   static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
   static __device__ __forceinline__ double rcp(double x) { return 1.0 / x; }
   static __device__ __forceinline__ double rsqrt(double x) { return 1.0 / ::sqrt(x); }
+  static __device__ __forceinline__ double rsqrt_near_one(double x) { return 1.0 / ::sqrt(x); }
   static __device__ __forceinline__ double fdiv(double a, double b) { return a / b; }
   static __device__ __forceinline__ double frcp(double x) { return 1.0 / x; }
   static __device__ __forceinline__ double cospi_unit(double x) { return ::cospi(x); }

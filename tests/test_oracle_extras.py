@@ -1,9 +1,40 @@
-"""CPU: sanity of the non-reference extensions in the oracle (aerodynamic extras, kinematic herd)."""
+"""CPU: the aerodynamic extras of the oracle against force vectors computed by the reference's own formulas, and
+sanity of the non-reference kinematic herd."""
+import os
+
 import numpy as np
 
 from _golden import Golden
 
 import cattle_oracle as co  # noqa: E402  (tests/_golden.py put oracle/ on sys.path)
+
+
+def test_aero_terms_match_forces_recorded_from_the_reference():
+    """tests/golden/aero/aero_forces.npz holds what the UNMODIFIED `_groundEffect`, `_drag`, `_downwash`
+    (sb3_envs/BaseAviary.py:943-1039) handed to `p.applyExternalForce` for 240 random states (recorded through the
+    stand-in by oracle/ref_harness/make_aero_golden.py).  `aero_terms`, the piece `_dynamics` adds to the DYN step,
+    has to reproduce every vector at 1e-12 (relative to the force scale) -- the CUDA tests then compare the device with
+    this restatement."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "aero", "aero_forces.npz"))
+    n_applied = n_gated = n_dw = 0
+    for s in range(z["pos"].shape[0]):
+        pos, quat, vel = z["pos"][s], z["quat"][s], z["vel"][s]
+        R = co.quat_to_matrix(tuple(quat[0]))
+        gnd, drag_w, dwz = co.aero_terms(7, pos[0], R, vel[0], z["rpm"][s], z["drag_rpm"][s], pos, 0, pos.shape[0])
+        ref_g = z["gnd_forces"][s]
+        assert np.allclose(gnd, ref_g, rtol=1e-12, atol=1e-18), (s, gnd, ref_g)
+        assert bool(z["gnd_applied"][s]) == (R[2][2] > 0)          # the |roll|, |pitch| < pi/2 gate (:970)
+        n_applied += int(z["gnd_applied"][s]); n_gated += int(not z["gnd_applied"][s])
+        # the reference hands R^T d to LINK_FRAME of the centre-of-mass link: rotate ours into the body frame
+        Rm = np.array(R)
+        assert np.allclose(Rm.T @ np.array(drag_w), z["drag_force"][s], rtol=1e-12, atol=1e-18), s
+        ref_dw = float(np.sum(z["downwash_forces"][s]))
+        assert abs(dwz - ref_dw) <= 1e-12 * max(1.0, abs(ref_dw)), (s, dwz, ref_dw)
+        n_dw += int(ref_dw != 0)
+    assert n_applied > 100 and n_gated > 20 and n_dw > 50
+    c = z["consts"]
+    assert np.allclose(c, [co.KF, co.GND_EFF_COEFF, co.PROP_RADIUS, co.GND_EFF_H_CLIP, co.DRAG_XY, co.DRAG_Z, co.DW1, co.DW2, co.DW3],
+                       rtol=1e-15)
 
 
 def test_aero_physics_sanity_of_the_restatement():
