@@ -42,6 +42,7 @@ extern "C" {
 #define CHS_ABI_VERSION 3
 #define CHS_MAX_DRONES 12   /* GLOBAL_MAX_NUM_DRONES, BaseAviary.py:112 */
 #define CHS_NUM_STATS 16
+#define CHS_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)   /* size of the static device array behind chs_step_static_scratch */
 
 typedef enum ChsStatus {
   CHS_OK = 0,
@@ -163,6 +164,23 @@ int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_dev, void* s
  * first observation of the new episode, as SB3's VecEnv contract requires. */
 int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, float* reward_dev,
              uint8_t* terminated_dev, uint8_t* truncated_dev, float* terminal_obs_dev, void* stream);
+
+/* No counterpart in the reference: added for callers that may not call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same control step, same arguments and same
+ * results as chs_step in split mode (step mode 2: drone_kernel, step_kernel, reset_list_kernel), but the scratch those
+ * kernels hand data through -- the per-drone (ang_v, yaw) rows between the first two and the list of finished envs between
+ * the last two -- lives in ONE file-scope `static __device__` array of CHS_STATIC_SCRATCH_BYTES (8 MiB) per GPU instead of
+ * buffers from cudaMalloc.  Every GPU that loads the library holds that array until the process exits.  The call itself
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library routine): kernel launches, a 256-byte cudaMemsetAsync and,
+ * with the downwash model only, one device-to-device copy.  The array's device address is looked up with
+ * cudaGetSymbolAddress by chs_create, once per device, with that device current.
+ * Limit: 256 + roundup256(4*E) + 16*D*E bytes (32*D*E in the fp64 build) must fit, e.g. E <= 161 000 envs at D = 3 drone
+ * slots, E <= 42 700 at D = 12; larger batches are rejected with CHS_ERR_INVALID and a message naming the limit.
+ * ALL handles of a process on one GPU share the array, and it keeps the previous call's contents (the call clears the one
+ * counter that has to start at zero): calls that overlap on the GPU -- two streams, two handles, or this call racing a graph
+ * replay of it -- corrupt each other; issue them in stream order.  Mixing with chs_step on the same handle is fine. */
+int chs_step_static_scratch(ChsHandle* h, const float* actions_dev, float* obs_dev, float* reward_dev,
+                            uint8_t* terminated_dev, uint8_t* truncated_dev, float* terminal_obs_dev, void* stream);
 
 /* Same step with HOST buffers (what a numpy-facing VecEnv calls): actions are copied H2D from
  * the handle's pinned staging area, results D2H, and the call returns after the stream has

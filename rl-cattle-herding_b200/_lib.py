@@ -11,6 +11,7 @@ LIB_PATH = os.environ.get("CHS_LIB", os.path.join(_HERE, "libchs.so"))   # CHS_L
 ABI_VERSION = 3
 MAX_DRONES = 12
 NUM_STATS = 16
+STATIC_SCRATCH_BYTES = 8 * 1024 * 1024
 
 STAT_NAMES = ("episodes", "sum_return", "sum_length", "terminated", "trunc_altitude", "trunc_collision",
               "trunc_formation", "trunc_boundary", "trunc_time_limit", "non_finite", "env_steps")
@@ -18,7 +19,8 @@ STAT_NAMES = ("episodes", "sum_return", "sum_length", "terminated", "trunc_altit
 # every symbol include/chs.h declares (checked by tests/test_abi.py)
 SYMBOLS = ("chs_abi_version", "chs_last_error", "chs_create", "chs_destroy", "chs_get_dims", "chs_set_spawn_table",
            "chs_reset", "chs_step", "chs_step_host", "chs_reset_host", "chs_get_state", "chs_set_state",
-           "chs_set_debug_buffers", "chs_set_phase_clock", "chs_set_step_mode", "chs_set_register_variant", "chs_stats", "chs_set_launch")
+           "chs_set_debug_buffers", "chs_set_phase_clock", "chs_set_step_mode", "chs_set_register_variant", "chs_stats", "chs_set_launch",
+           "chs_step_static_scratch")
 
 
 class ChsParams(C.Structure):
@@ -69,6 +71,7 @@ def load():
     lib.chs_set_spawn_table.argtypes = [vp, vp, i32, i32]
     lib.chs_reset.argtypes = [vp, vp, vp, vp]
     lib.chs_step.argtypes = [vp] * 8
+    lib.chs_step_static_scratch.argtypes = [vp] * 8
     lib.chs_step_host.argtypes = [vp] * 10
     lib.chs_reset_host.argtypes = [vp, vp, vp, vp]
     lib.chs_get_state.argtypes = [vp, i32, i32, C.POINTER(ChsStateView)]

@@ -160,6 +160,18 @@ class CattleHerdingBatchedEnv:
                                      _ptr(self.truncated), _ptr(tobs), self._stream()))
         return self.obs, self.reward, self.terminated, self.truncated
 
+    def step_static_scratch(self, actions, want_terminal_obs=True):
+        """`step()` through `chs_step_static_scratch`: the split-mode kernels with their scratch in the library's static
+        device array (8 MiB per GPU, shared by every env object of the process), for callers that must not allocate.
+        Raises if the batch does not fit; calls that overlap on the GPU race on the array."""
+        if actions.dtype != torch.float32 or not actions.is_cuda or not actions.is_contiguous():
+            actions = actions.to(device=self.device, dtype=torch.float32).contiguous()
+        assert actions.numel() == self.num_envs * self.max_drones * self.action_width, "actions must be (E, D, A)"
+        tobs = self.terminal_obs if (want_terminal_obs and self.auto_reset) else None
+        _lib.check(self.lib.chs_step_static_scratch(self._h, _ptr(actions), _ptr(self.obs), _ptr(self.reward),
+                                                    _ptr(self.terminated), _ptr(self.truncated), _ptr(tobs), self._stream()))
+        return self.obs, self.reward, self.terminated, self.truncated
+
     # ---- host-buffer path (numpy in / numpy out; what a VecEnv calls) --------------------------------
     def _host_buffers(self):
         if self._host is None:

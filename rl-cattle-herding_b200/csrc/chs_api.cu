@@ -87,6 +87,30 @@ struct DeviceGuard {
   ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// ---- static scratch for chs_step_static_scratch (no counterpart in the reference; added
+// for callers that may not call cudaMalloc: code under CUDA graph capture, tight serving loops) -----------------
+// One file-scope device array per GPU that loads this library, held until the process exits.  In HOST code the name
+// `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per device with
+// that device current (resolve_static_scratch, called from chs_create) and that pointer is what the kernels receive.
+// Layout used by a call:  [0, 256) finished-env counter | [256, 256 + 4E rounded up to 256) finished-env list |
+//                         D*E 4-vectors of the split step's (ang_v, yaw) hand-over between drone_kernel and step_kernel.
+static __device__ __align__(256) unsigned char g_static_scratch[CHS_STATIC_SCRATCH_BYTES];
+
+static const int kMaxDevices = 64;
+static void* g_static_scratch_addr[kMaxDevices] = {nullptr};
+
+// Caller has made `device` current.  Idempotent; no allocation (the array is part of the loaded module image).
+static int resolve_static_scratch(int device) {
+  if (device < 0 || device >= kMaxDevices) return fail(CHS_ERR_INVALID, "device %d outside the static-scratch table", device);
+  if (g_static_scratch_addr[device]) return CHS_OK;
+  void* ptr = nullptr;
+  const cudaError_t err = cudaGetSymbolAddress(&ptr, g_static_scratch);
+  if (err != cudaSuccess || !ptr)
+    return fail(CHS_ERR_CUDA, "cudaGetSymbolAddress(g_static_scratch) failed on device %d: %s", device, cudaGetErrorString(err));
+  g_static_scratch_addr[device] = ptr;
+  return CHS_OK;
+}
+
 extern "C" int chs_abi_version(void) { return CHS_ABI_VERSION; }
 extern "C" const char* chs_last_error(void) { return g_err; }
 
@@ -245,6 +269,8 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
     chs_destroy(h);
     return fail(CHS_ERR_CUDA, "device allocation failed: %s", cudaGetErrorString(err));
   }
+  // set-up of the static scratch used by chs_step_static_scratch: symbol address for THIS device (current via `dg`)
+  { const int src = resolve_static_scratch(device); if (src != CHS_OK) { chs_destroy(h); return src; } }
   // env scalars: level = start level, prev_cent_dist = None (NaN), everything else zero
   {
     std::vector<int4> ej(E);
@@ -475,6 +501,66 @@ extern "C" int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, 
                                              terminal_obs_dev, 1, nullptr, nullptr, (cudaStream_t)stream);
   nvtx_pop();
   return rc;
+}
+
+// ---- chs_step_static_scratch ------------------------------------------------------------------------------------------
+// The split-mode control step (drone_kernel -> step_kernel<SPLIT> -> reset_list_kernel, the same kernels chs_step launches in
+// step mode 2) with its scratch -- the drone-to-task hand-over rows and the finished-env list -- in g_static_scratch instead of
+// the handle's cudaMalloc'ed buffers.  Calls no cudaMalloc / cudaFree / allocating routine: kernel launches, one
+// cudaMemsetAsync of the 256-byte counter block and (downwash only) one device-to-device copy into a buffer chs_create made.
+template <typename T>
+static int launch_step_static(ChsHandle* h, unsigned char* scratch, const float* actions, float* obs, float* reward, uint8_t* term,
+                              uint8_t* trunc, float* term_obs, cudaStream_t st) {
+  const size_t E = (size_t)h->E, D = (size_t)h->kp.D;
+  const size_t list_off = 256, list_bytes = (E * sizeof(int) + 255) & ~(size_t)255;
+  const size_t own_off = list_off + list_bytes, own_bytes = D * E * 4 * sizeof(T);
+  if (own_off + own_bytes > (size_t)CHS_STATIC_SCRATCH_BYTES)
+    return fail(CHS_ERR_INVALID, "chs_step_static_scratch: %zu envs x %zu drone slots need %zu bytes of scratch, the static array "
+                "holds CHS_STATIC_SCRATCH_BYTES = %d; use chs_step for larger batches", E, D, own_off + own_bytes, CHS_STATIC_SCRATCH_BYTES);
+  KArgs<T> a = base_args<T>(h);
+  a.actions = actions; a.obs = obs; a.reward = reward; a.terminated = term; a.truncated = trunc;
+  a.term_obs = term_obs; a.term_mode = term_obs ? 1 : 0;
+  a.own2 = reinterpret_cast<typename VT<T>::v4*>(scratch + own_off);
+  int* count = reinterpret_cast<int*>(scratch);
+  int* list = reinterpret_cast<int*>(scratch + list_off);
+  // the array keeps the previous call's contents: the counter has to start at zero (the hand-over rows and the list are
+  // written before they are read, for exactly the entries that are read)
+  CUDA_TRY(cudaMemsetAsync(scratch, 0, 256, st));
+  if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, D * E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
+  const bool defer = h->kp.auto_reset != 0;
+  if (defer) a.done_count = count;
+  const long long nthr = (long long)D * (long long)E;
+  drone_kernel<T><<<(unsigned)((nthr + 255) / 256), 256, 0, st>>>(a);
+  a.p.split = 1;
+  if (defer) { a.done_list = list; a.done_count = count; }
+  const int grid = (h->E + h->kp.G - 1) / h->kp.G;
+  launch_step_variant<T>(h, a, grid, st);
+  if (defer) {
+    KArgs<T> r = base_args<T>(h);
+    r.done_list = list; r.done_count = count; r.obs = obs;
+    reset_list_kernel<T><<<148 * 8, 256, 0, st>>>(r);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return CHS_OK;
+}
+
+extern "C" int chs_step_static_scratch(ChsHandle* h, const float* actions_dev, float* obs_dev, float* reward_dev,
+                                       uint8_t* terminated_dev, uint8_t* truncated_dev, float* terminal_obs_dev, void* stream) {
+  if (!h) return fail(CHS_ERR_INVALID, "null handle");
+  if (!actions_dev || !reward_dev || !terminated_dev || !truncated_dev)
+    return fail(CHS_ERR_INVALID, "actions, reward, terminated and truncated pointers are required");
+  if (h->kp.auto_reset && !h->spawn_set) return fail(CHS_ERR_STATE, "auto_reset needs a spawn table");
+  if (h->kp.act4_ok && !aligned16(actions_dev)) return fail(CHS_ERR_INVALID, "actions_dev must be 16-byte aligned");
+  if (h->kp.vec4_ok && ((obs_dev && !aligned16(obs_dev)) || (terminal_obs_dev && !aligned16(terminal_obs_dev))))
+    return fail(CHS_ERR_INVALID, "obs buffers must be 16-byte aligned");
+  if (h->device < 0 || h->device >= kMaxDevices || !g_static_scratch_addr[h->device])
+    return fail(CHS_ERR_STATE, "static scratch address of device %d was not resolved at chs_create", h->device);
+  DeviceGuard dg(h->device);
+  unsigned char* scratch = static_cast<unsigned char*>(g_static_scratch_addr[h->device]);   // the looked-up device address, never the symbol
+  return h->f64 ? launch_step_static<double>(h, scratch, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
+                                             terminal_obs_dev, (cudaStream_t)stream)
+                : launch_step_static<float>(h, scratch, actions_dev, obs_dev, reward_dev, terminated_dev, truncated_dev,
+                                            terminal_obs_dev, (cudaStream_t)stream);
 }
 
 #include "chs_api_io.inc"
