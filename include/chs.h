@@ -158,7 +158,9 @@ int chs_set_spawn_table(ChsHandle* h, const double* xy_host, int32_t n_sims, int
  * initial observation of those envs into obs_dev (may be NULL). */
 int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_dev, void* stream);
 
-/* BaseAviary.step (:335-465): one control step of every env in ONE kernel launch.
+/* BaseAviary.step (:335-465): one control step of every env.  Step mode 1 (fused) is ONE kernel launch; step mode 2
+ * (split, picked automatically for batches several waves deep) is drone_kernel + step_kernel + reset_list_kernel, plus one
+ * device-to-device copy when the downwash model is on (see chs_set_step_mode).
  * terminal_obs_dev (nullable): [E][R][L]; with auto_reset the pre-reset observation of each
  * finished env is written there (rows of other envs are left untouched) and obs_dev receives the
  * first observation of the new episode, as SB3's VecEnv contract requires. */
@@ -199,6 +201,11 @@ int chs_reset_host(ChsHandle* h, const uint8_t* env_mask_host, float* obs_host, 
 int chs_get_state(ChsHandle* h, int32_t env0, int32_t count, ChsStateView* out_host);
 int chs_set_state(ChsHandle* h, int32_t env0, int32_t count, const ChsStateView* in_host);
 
+/* BaseAviary.NUM_DRONES of every env (BaseAviary.py:242,307: drawn per episode) as int32 [E] on the device: one
+ * stream-ordered device-to-device copy, no kernel, no allocation.  A MARL learner uses it to tell drone slots that exist from
+ * padding slots (rllib_envs/BaseAviary.py:425-430 builds its dicts over range(NUM_DRONES) only). */
+int chs_get_num_drones(ChsHandle* h, int32_t* n_drones_dev, void* stream);
+
 /* Optional integer diagnostics written by chs_step (bit-exact parity outputs): the indices of the two
  * nearest drones per drone as ranked by _computeObs (BaseRLAviary.py:310-311), int32 [E][D][2],
  * and the herded-cow count of evaluate_herding_effectiveness (utils/evaluation.py:100-138),
@@ -213,7 +220,8 @@ int chs_set_register_variant(ChsHandle* h, int32_t variant);
 /* How chs_step maps onto kernels: 1 = fused, one launch per control step (drone chains on the first warps of every
  * CTA, the herd on the others: the shortest path for batches of about one wave); 2 = split, two launches
  * (drone_kernel: one thread per drone, no shared memory, no barrier; step_kernel: herd, task layer, observation);
- * 0 = chosen by batch size (default).  Results are bit-identical between the modes. */
+ * 0 = chosen by batch size (default).  Results are bit-identical between the modes in the fp64 build and equal up to fp32
+ * contraction in the fp32 build (two compilations of the same device functions). */
 int chs_set_step_mode(ChsHandle* h, int32_t mode);
 
 /* Profiling aid: when non-NULL, thread 0 of every CTA of chs_step writes clock64() at the 7 phase boundaries

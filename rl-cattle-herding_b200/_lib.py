@@ -20,7 +20,7 @@ STAT_NAMES = ("episodes", "sum_return", "sum_length", "terminated", "trunc_altit
 SYMBOLS = ("chs_abi_version", "chs_last_error", "chs_create", "chs_destroy", "chs_get_dims", "chs_set_spawn_table",
            "chs_reset", "chs_step", "chs_step_host", "chs_reset_host", "chs_get_state", "chs_set_state",
            "chs_set_debug_buffers", "chs_set_phase_clock", "chs_set_step_mode", "chs_set_register_variant", "chs_stats", "chs_set_launch",
-           "chs_step_static_scratch")
+           "chs_step_static_scratch", "chs_get_num_drones")
 
 
 class ChsParams(C.Structure):
@@ -77,6 +77,7 @@ def load():
     lib.chs_get_state.argtypes = [vp, i32, i32, C.POINTER(ChsStateView)]
     lib.chs_set_state.argtypes = [vp, i32, i32, C.POINTER(ChsStateView)]
     lib.chs_set_debug_buffers.argtypes = [vp, vp, vp]
+    lib.chs_get_num_drones.argtypes = [vp, vp, vp]
     lib.chs_set_phase_clock.argtypes = [vp, vp]
     lib.chs_set_register_variant.argtypes = [vp, i32]
     lib.chs_set_step_mode.argtypes = [vp, i32]

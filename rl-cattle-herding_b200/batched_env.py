@@ -160,6 +160,14 @@ class CattleHerdingBatchedEnv:
                                      _ptr(self.truncated), _ptr(tobs), self._stream()))
         return self.obs, self.reward, self.terminated, self.truncated
 
+    def num_drones_dev(self):
+        """`NUM_DRONES` of every env as an int32 CUDA tensor (E,) owned by this object (stream-ordered copy of the
+        simulator's per-env scalar; BaseAviary.py:307 draws it per episode)."""
+        if getattr(self, "_ndr", None) is None:
+            self._ndr = torch.zeros((self.num_envs,), dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.chs_get_num_drones(self._h, _ptr(self._ndr), self._stream()))
+        return self._ndr
+
     def step_static_scratch(self, actions, want_terminal_obs=True):
         """`step()` through `chs_step_static_scratch`: the split-mode kernels with their scratch in the library's static
         device array (8 MiB per GPU, shared by every env object of the process), for callers that must not allocate.

@@ -387,6 +387,15 @@ extern "C" int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev) {
   return CHS_OK;
 }
 
+extern "C" int chs_get_num_drones(ChsHandle* h, int32_t* n_drones_dev, void* stream) {
+  if (!h || !n_drones_dev) return fail(CHS_ERR_INVALID, "null argument");
+  DeviceGuard dg(h->device);
+  // envi[e] = (step_counter, step_counter_A, n_drones, spawn_idx): column 2 of an [E][4] int32 matrix
+  CUDA_TRY(cudaMemcpy2DAsync(n_drones_dev, sizeof(int32_t), reinterpret_cast<const char*>(h->envi) + 2 * sizeof(int32_t), sizeof(int4),
+                             sizeof(int32_t), (size_t)h->E, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return CHS_OK;
+}
+
 extern "C" int chs_set_debug_buffers(ChsHandle* h, int32_t* neighbors_dev, int32_t* herded_dev) {
   if (!h) return fail(CHS_ERR_INVALID, "null handle");
   h->dbg_nb = neighbors_dev; h->dbg_herd = herded_dev;

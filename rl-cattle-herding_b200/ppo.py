@@ -95,6 +95,35 @@ def gae(rewards, values, dones, last_values, gamma, lam):
     return adv, adv + values
 
 
+def ppo_loss(policy, obs, act, old_logp, adv, ret, w, hp):
+    """SB3 `PPO.train` loss of one minibatch with per-sample weights `w` (1 = a sample that exists, 0 = padding).
+    With all weights 1 this is SB3's loss exactly (per-minibatch advantage normalisation with the unbiased std, clipped
+    surrogate, MSE value loss, entropy bonus); a sample with weight 0 contributes to no mean, to no normalisation
+    statistic and to no gradient, whatever its contents (they are replaced before any arithmetic, so NaN padding is
+    harmless).  Returns (loss, pg, vf, ent, clipfrac)."""
+    live = w > 0
+    n = w.sum().clamp_min(1.0)
+    adv = torch.where(live, adv, torch.zeros_like(adv))
+    ret = torch.where(live, ret, torch.zeros_like(ret))
+    old_logp = torch.where(live, old_logp, torch.zeros_like(old_logp))
+    obs = torch.where(live[:, None], obs, torch.zeros_like(obs))
+    act = torch.where(live[:, None], act, torch.zeros_like(act))
+    if adv.numel() > 1:
+        mean = (adv * w).sum() / n
+        var = (((adv - mean) ** 2) * w).sum() / (n - 1.0).clamp_min(1.0)
+        adv = (adv - mean) / (var.sqrt() + 1e-8)
+    mu, log_std = policy.dist(obs)
+    logp = policy.log_prob(mu, log_std, act)
+    ratio = torch.exp(logp - old_logp)
+    surr = torch.min(adv * ratio, adv * ratio.clamp(1 - hp["clip_range"], 1 + hp["clip_range"]))
+    pg = -(surr * w).sum() / n
+    vf = (((ret - policy.value(obs)) ** 2) * w).sum() / n
+    ent = -policy.entropy(log_std).mean()              # state-independent log-std: the same for every sample
+    loss = pg + hp["ent_coef"] * ent + hp["vf_coef"] * vf
+    clipfrac = ((((ratio.detach() - 1).abs() > hp["clip_range"]).float()) * w).sum() / n
+    return loss, pg, vf, ent, clipfrac
+
+
 def average_gradients(params):
     """One all-reduce of the flattened gradients across the process group (no-op without torch.distributed)."""
     import torch.distributed as dist
@@ -153,7 +182,9 @@ class DevicePPO:
         f = dict(dtype=torch.float32, device=dev)
         self.buf = dict(obs=torch.zeros((T, B, self.obs_dim), **f), act=torch.zeros((T, B, self.act_dim), **f),
                         logp=torch.zeros((T, B), **f), val=torch.zeros((T, B), **f), rew=torch.zeros((T, B), **f),
-                        done=torch.zeros((T, B), **f), adv=torch.zeros((T, B), **f), ret=torch.zeros((T, B), **f))
+                        done=torch.zeros((T, B), **f), adv=torch.zeros((T, B), **f), ret=torch.zeros((T, B), **f),
+                        w=torch.ones((T, B), **f))      # 1 = the sample's drone slot exists (MARL: slot < NUM_DRONES of its env)
+        self._slot = torch.arange(D, dtype=torch.int32, device=dev)
         self._idx = torch.zeros((self.batch_size,), dtype=torch.long, device=dev)
         self._acc = torch.zeros((4,), **f)            # sums of pg, vf, ent, clipfrac over the minibatches of an update
         self.num_timesteps = 0
@@ -183,6 +214,11 @@ class DevicePPO:
         env, buf, hp = self.env, self.buf, self.hp
         for t in range(self.n_steps):
             a, logp, v = self.policy.act(self._obs)
+            if self.marl:
+                # the reference's RLlib loop only ever sees agents that exist (rllib_envs/BaseAviary.py:425-430 build the
+                # dicts over range(NUM_DRONES)); slots >= NUM_DRONES of a fixed-shape batch are padding, not samples
+                n = env.num_drones_dev()
+                buf["w"][t].copy_((self._slot[None, :] < n[:, None]).reshape(self.B))
             buf["obs"][t].copy_(self._obs)
             buf["act"][t].copy_(a)
             buf["logp"][t].copy_(logp)
@@ -193,7 +229,8 @@ class DevicePPO:
             # time-limit truncation: bootstrap with the value of the terminal observation
             # (OnPolicyAlgorithm.collect_rollouts: rewards[idx] += gamma * predict_values(terminal_observation))
             tv = self.policy.value(self._flat_obs(env.terminal_obs))
-            buf["rew"][t].copy_(rew.reshape(self.B) + hp["gamma"] * tv * boot)
+            # where(): a stale terminal_obs row of an env that did not finish may hold anything, and NaN * 0 is NaN
+            buf["rew"][t].copy_(rew.reshape(self.B) + hp["gamma"] * torch.where(boot > 0, tv, torch.zeros_like(tv)))
             buf["done"][t].copy_(done)
             self._obs.copy_(self._flat_obs(obs))      # episode statistics come from the simulator's accumulator (env.stats)
         last_v = self.policy.value(self._obs)
@@ -228,16 +265,8 @@ class DevicePPO:
         hp, buf = self.hp, self.buf
         N = self.n_steps * self.B
         obs, act = buf["obs"].reshape(N, -1), buf["act"].reshape(N, -1)
-        a_mb = buf["adv"].reshape(N)[idx]
-        if idx.numel() > 1:
-            a_mb = (a_mb - a_mb.mean()) / (a_mb.std() + 1e-8)      # per-minibatch, like SB3
-        mean, log_std = self.policy.dist(obs[idx])
-        logp = self.policy.log_prob(mean, log_std, act[idx])
-        ratio = torch.exp(logp - buf["logp"].reshape(N)[idx])
-        pg = -torch.min(a_mb * ratio, a_mb * ratio.clamp(1 - hp["clip_range"], 1 + hp["clip_range"])).mean()
-        vf = torch.nn.functional.mse_loss(buf["ret"].reshape(N)[idx], self.policy.value(obs[idx]))
-        ent = -self.policy.entropy(log_std).mean()
-        loss = pg + hp["ent_coef"] * ent + hp["vf_coef"] * vf
+        loss, pg, vf, ent, clipfrac = ppo_loss(self.policy, obs[idx], act[idx], buf["logp"].reshape(N)[idx], buf["adv"].reshape(N)[idx],
+                                               buf["ret"].reshape(N)[idx], buf["w"].reshape(N)[idx], hp)
         self.opt.zero_grad(set_to_none=True)
         loss.backward()
         average_gradients(self._params)
@@ -245,8 +274,7 @@ class DevicePPO:
             nn.utils.clip_grad_norm_(self._params, hp["max_grad_norm"])
         self.opt.step()
         with torch.no_grad():
-            self._acc += torch.stack([pg.detach(), vf.detach(), ent.detach(),
-                                      ((ratio.detach() - 1).abs() > hp["clip_range"]).float().mean()])
+            self._acc += torch.stack([pg.detach(), vf.detach(), ent.detach(), clipfrac.detach()])
 
     def _capture_update(self):
         """Whole-step capture (PyTorch CUDA-graph recipe): a few eager steps on a side stream, whose effect on the
@@ -294,7 +322,8 @@ class DevicePPO:
                 n_mb += 1
         acc = (self._acc / max(1, n_mb)).tolist()
         self.last = dict(pg=acc[0], vf=acc[1], ent=acc[2], clipfrac=acc[3])
-        ret_f, val_f = buf["ret"].reshape(N), buf["val"].reshape(N)
+        live = buf["w"].reshape(N) > 0
+        ret_f, val_f = buf["ret"].reshape(N)[live], buf["val"].reshape(N)[live]
         self.last["explained_variance"] = float(1 - (ret_f - val_f).var() / (ret_f.var() + 1e-8))
         return self.last
 

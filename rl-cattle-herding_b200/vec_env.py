@@ -94,6 +94,7 @@ class GpuCattleVecEnv(_VecEnvBase):
         self.CTRL_TIMESTEP = 1.0 / ctrl_freq
         self._actions = None
         self._seed = seed
+        self._shared_info = {"answer": 42}     # shared by the envs that did not finish a step: treat as read-only
 
     # ---- VecEnv contract --------------------------------------------------------------------------------
     def reset(self):
@@ -105,11 +106,13 @@ class GpuCattleVecEnv(_VecEnvBase):
     def step_wait(self):
         obs, rew, term, trunc, done_idx, term_obs = self.sim.step_host(self._actions)
         dones = (term | trunc).astype(bool)
-        infos = [{} for _ in range(self.num_envs)]
+        # E Python dicts per step would dominate a 4096-env rollout: envs that did not finish share ONE info dict
+        # (`CattleAviary._computeInfo` returns the constant {"answer": 42}, :557-568; SB3 only reads infos of finished
+        # envs and copies before it writes), finished envs get their own
+        infos = [self._shared_info] * self.num_envs
         for r, e in enumerate(done_idx):
-            infos[e]["terminal_observation"] = term_obs[r].copy()
-            infos[e]["TimeLimit.truncated"] = bool(trunc[e]) and not bool(term[e])
-            infos[e]["answer"] = 42          # CattleAviary._computeInfo (:557-568)
+            infos[e] = {"answer": 42, "terminal_observation": term_obs[r].copy(),
+                        "TimeLimit.truncated": bool(trunc[e]) and not bool(term[e])}
         return obs.copy(), rew.copy(), dones, infos
 
     def close(self):

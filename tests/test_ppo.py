@@ -50,6 +50,46 @@ def test_policy_shapes_and_distribution():
     assert torch.allclose(log_std, torch.full((12,), -1.0))
 
 
+def test_loss_equals_sb3_formula_and_ignores_padding_samples():
+    """All weights 1: SB3's `PPO.train` loss written out.  Weight 0 (MARL slots >= NUM_DRONES): the sample's contents,
+    NaN included, change neither the loss nor any gradient (phantom agents entered the loss)."""
+    torch.manual_seed(1)
+    pol = ppo.MlpActorCritic(66, 4, (32, 32), 0.0).double()
+    hp = dict(ppo.RLLIB_DTDE)
+    n = 40
+    obs, act = torch.randn(n, 66, dtype=torch.float64), torch.randn(n, 4, dtype=torch.float64)
+    old, adv, ret = torch.randn(n, dtype=torch.float64) - 4, torch.randn(n, dtype=torch.float64), torch.randn(n, dtype=torch.float64)
+    loss, pg, vf, ent, cf = ppo.ppo_loss(pol, obs, act, old, adv, ret, torch.ones(n, dtype=torch.float64), hp)
+    a = (adv - adv.mean()) / (adv.std() + 1e-8)
+    mu, ls = pol.dist(obs)
+    ratio = torch.exp(pol.log_prob(mu, ls, act) - old)
+    pg_ref = -torch.min(a * ratio, a * ratio.clamp(1 - hp["clip_range"], 1 + hp["clip_range"])).mean()
+    vf_ref = torch.nn.functional.mse_loss(ret, pol.value(obs))
+    assert torch.allclose(pg, pg_ref, atol=1e-12) and torch.allclose(vf, vf_ref, atol=1e-12)
+    assert torch.allclose(loss, pg_ref + hp["ent_coef"] * (-pol.entropy(ls).mean()) + hp["vf_coef"] * vf_ref, atol=1e-12)
+    # 15 padding samples with garbage spliced in between the real ones
+    m = n + 15
+    keep = torch.randperm(m)[:n].sort().values
+    w = torch.zeros(m, dtype=torch.float64); w[keep] = 1
+
+    def pad(x, fill):
+        out = torch.full((m,) + x.shape[1:], fill, dtype=torch.float64)
+        out[keep] = x
+        return out
+    grads = []
+    for fill in (0.0, 1e6, float("nan")):
+        pol.zero_grad()
+        l2, pg2, vf2, _, cf2 = ppo.ppo_loss(pol, pad(obs, fill), pad(act, fill), pad(old, fill), pad(adv, fill), pad(ret, fill), w, hp)
+        l2.backward()
+        assert torch.allclose(l2, loss, atol=1e-12) and torch.allclose(pg2, pg, atol=1e-12) and torch.allclose(cf2, cf, atol=1e-12), fill
+        grads.append([p.grad.clone() for p in pol.parameters()])
+    pol.zero_grad()
+    loss.backward()
+    for g in grads:
+        for a_, b_ in zip(g, pol.parameters()):
+            assert torch.isfinite(a_).all() and torch.allclose(a_, b_.grad, atol=1e-10)
+
+
 def test_reference_hyperparameters():
     """simulator/CTDECattleHerder.py:107-127 and simulator/DTDECattleHerder.py:84-93."""
     h = ppo.SB3_CTDE
@@ -80,4 +120,37 @@ def test_short_training_run(packing):
     # done flags in the last rollout = episodes the simulator's own accumulator counted during it
     per_env = algo.buf["done"].sum() / (N if packing == "marl" else 1)
     assert float(per_env) == hist[-1]["episodes"]
+    env.close()
+
+
+@pytest.mark.gpu
+def test_marl_padding_slots_are_not_samples():
+    """4 drone slots, level 0 => 3 drones per episode: slot 3 of every env is padding.  Its weight is 0 in the rollout
+    buffer and poisoning its stored observation / advantage changes nothing in the update."""
+    E, D, M = 128, 4, 20
+    env = pkg.CattleHerdingBatchedEnv(E, num_drones=D, num_cattle=M, ctrl_freq=30, start_level=0, packing="marl",
+                                      spawn_table=pkg.spawn.generate(16, M, seed=0), device=0, seed=0)
+    algo = ppo.DevicePPO(env, n_steps=6, seed=0, n_epochs=1, cuda_graphs=False)
+    algo.collect()
+    w = algo.buf["w"].reshape(6, E, D)
+    assert torch.equal(w[:, :, :3], torch.ones_like(w[:, :, :3])) and torch.equal(w[:, :, 3], torch.zeros_like(w[:, :, 3]))
+    assert torch.isfinite(algo.buf["rew"]).all()
+    state = [p.detach().clone() for p in algo.policy.parameters()]
+    torch.manual_seed(5)
+    algo.update()
+    after_clean = [p.detach().clone() for p in algo.policy.parameters()]
+    with torch.no_grad():
+        for p, q in zip(algo.policy.parameters(), state):
+            p.copy_(q)
+        for st in algo.opt.state.values():
+            for v in st.values():
+                if torch.is_tensor(v):
+                    v.zero_()
+    algo.buf["obs"].reshape(6, E, D, -1)[:, :, 3] = float("nan")
+    algo.buf["adv"].reshape(6, E, D)[:, :, 3] = 1e9
+    algo.buf["ret"].reshape(6, E, D)[:, :, 3] = -1e9
+    torch.manual_seed(5)
+    algo.update()
+    for a, b in zip(after_clean, algo.policy.parameters()):
+        assert torch.isfinite(b).all() and torch.allclose(a, b.detach(), atol=1e-6)
     env.close()
