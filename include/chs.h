@@ -93,6 +93,11 @@ typedef struct ChsParams {
                                  CALLER: chs_reset writes them for the envs it resets, chs_step never touches them (3/4 of
                                  the bytes of a (12, 66) image at 3 drones).  Buffers handed to chs_step -- obs_dev and
                                  terminal_obs_dev -- must hold zeros there (zero-fill them once, or chs_reset into them).
+                                 Granularity is 16 bytes: the store of the live rows may rewrite (with zeros) up to 12 bytes
+                                 at the start of row max_drones.  On the pinned-host path (chs_step_host / chs_reset_host)
+                                 the same holds for the dead columns of the live rows in the sb3 packing: neighbour slots
+                                 2..11 (columns 14..33, BaseRLAviary.py:313-314 pads 2 active neighbours to 12 slots) are
+                                 zeros that chs_reset_host writes and chs_step_host skips (fewer bytes across PCIe).
                                  0: every call rewrites the full image (the reference's _computeObs does, BaseRLAviary.py:334) */
   int32_t reserved1;
   uint64_t seed;              /* Philox key; streams are keyed by (seed, global env id, episode) */

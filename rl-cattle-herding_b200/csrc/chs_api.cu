@@ -79,6 +79,11 @@ struct ChsHandle {
   float *d_actions, *d_obs, *d_reward, *d_termobs;
   uint8_t *d_term, *d_trunc, *d_mask;
   int *d_count, *d_idx;
+  bool obs_dst_is_host;             // set by chs_step_host around its launch: obs / terminal obs point into pinned host memory
+  int* count_next;                  // host path: the ping-pong partner of the counter in use (zeroed by the launch)
+  unsigned host_calls;
+  struct { const void* host; void* dev; } alias_cache[4];   // pinned host buffer -> device alias (chs_api_io.inc)
+  unsigned alias_next;
 };
 
 struct DeviceGuard {
@@ -228,6 +233,12 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   kp.bulk_ok = (kp.vec4_ok && !getenv("CHS_NO_BULK")) ? 1 : 0;
   // persistent padding needs real padding rows and float4-addressable images (the reset kernel zero-fills them)
   kp.pad_persist = (prm->persistent_padding && R > prm->max_drones && kp.vec4_ok) ? 1 : 0;
+  // dead columns of a live row under the same contract: neighbour slots 2..11 of the sb3 observation (cols 14..33)
+  kp.dead_lo = kp.dead_hi = 0;
+  if (prm->persistent_padding && kp.bulk_ok && kp.packing == CHS_PACK_CTDE && kp.L >= 10 + 2 * CHS_MAX_DRONES && !getenv("CHS_NO_DEAD_SKIP")) {
+    kp.dead_lo = 10 + 2 * 2;                 // own state + active_neighbors = 2 slots (BaseAviary.py:117)
+    kp.dead_hi = 10 + 2 * CHS_MAX_DRONES;    // padded to GLOBAL_MAX_NUM_DRONES slots (BaseRLAviary.py:313-314)
+  }
   {
     const int total = kp.R * kp.L * 4, c1 = kp.stage_stride * 4 < total ? kp.stage_stride * 4 : total;
     kp.zero_bytes = (kp.bulk_ok && !kp.pad_persist) ? total - c1 : 0;
@@ -471,6 +482,10 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   KArgs<T> a = base_args<T>(h);
   a.actions = actions; a.obs = obs; a.reward = reward; a.terminated = term; a.truncated = trunc;
   a.term_obs = term_obs; a.term_mode = term_obs ? term_mode : 0; a.term_count = term_count; a.term_idx = term_idx;
+  a.term_count_next = (term_obs && term_mode == 2) ? h->count_next : nullptr;
+  // dead-column skipping pays on the PCIe path only (fewer bytes per env); in HBM the extra, smaller bulk stores cost more
+  // than the bytes they save (measured: 243 -> 294 us at 262 144 envs), so device destinations get the rows in one piece
+  if (!h->obs_dst_is_host) a.p.dead_lo = a.p.dead_hi = 0;
   const int grid = (h->E + h->kp.G - 1) / h->kp.G;
   // split mode: the drones get their own barrier-free kernel; auto picks it once the batch is several waves deep
   const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 1024);

@@ -84,6 +84,31 @@ __device__ __forceinline__ void bulk_copy_rows(const KParams& p, const float* st
   if (total > c1 && !p.pad_persist) bulk_store(reinterpret_cast<char*>(dst) + c1, zeros, total - c1);
 }
 
+// The staged live rows of one env to its image, skipping -- under the persistent-padding contract -- the 16-byte aligned
+// interior of each row's dead column range (12 - 2 unused neighbour slots = 80 of 264 bytes per row at L = 66): the row
+// tail and the next row's head are contiguous, so D rows leave as D + 1 bulk stores.  26 % fewer bytes per env at 3 drones,
+// which is what bounds the host path (the stores cross PCIe) and the large batches (HBM).
+__device__ __forceinline__ void bulk_store_live(const KParams& p, const float* stage_g, float* dst) {
+  const unsigned total = (unsigned)(p.R * p.L) * 4u;
+  unsigned c1 = (unsigned)p.stage_stride * 4u;
+  if (c1 > total) c1 = total;
+  const char* src = reinterpret_cast<const char*>(stage_g);
+  char* out = reinterpret_cast<char*>(dst);
+  unsigned cur = 0;
+  if (p.dead_hi > p.dead_lo) {
+    const unsigned rowb = (unsigned)p.L * 4u;
+    for (int d = 0; d < p.D; ++d) {
+      const unsigned a = ((unsigned)d * rowb + (unsigned)p.dead_lo * 4u + 15u) & ~15u;
+      const unsigned b = ((unsigned)d * rowb + (unsigned)p.dead_hi * 4u) & ~15u;
+      if (b > a && b <= c1) {
+        if (a > cur) bulk_store(out + cur, src + cur, a - cur);
+        cur = b;
+      }
+    }
+  }
+  if (c1 > cur) bulk_store(out + cur, src + cur, c1 - cur);
+}
+
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -803,11 +828,18 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   }
   CHS_STAMP(19);
   {
+    // cattle pieces: C lanes per (drone, env) item, as many as the CTA has threads for (up to 8), on threads half a CTA away
+    // from the drone warps; every thread runs the same number of rounds (the lanes of an item meet in shuffles)
     const int half = (nt >> 1) & ~31;
     const int tb = (t >= half) ? t - half : t + nt - half;
-    for (int it = tb; it < DG; it += nt) {
-      const int g = it & (G - 1), d = it >> lg, e = e0 + g;
-      if (e < E && d < s.n[g]) drone_cattle<T>(p, g, d, true, s.dpos, s.cpos, s.redB, s.stage);
+    int lc = 3;
+    while (lc > 0 && (DG << lc) > nt) --lc;
+    const int C = 1 << lc, items = DG << lc;
+    for (int base = 0; base < items; base += nt) {
+      const int idx = base + tb, it = idx >> lc, sub = idx & (C - 1);
+      const int g = it & (G - 1), d = it >> lg;
+      const bool valid = idx < items && e0 + g < E && d < s.n[g];
+      drone_cattle_coop<T>(p, valid, g, d, sub, C, true, s.dpos, s.cpos, s.redB, s.stage);
     }
   }
   CHS_STAMP(20);
@@ -842,7 +874,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   if (obs_lane) {
     const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_stride * 4u;
     fence_async_smem();
-    bulk_store(a.obs + (size_t)(e0 + ow) * p.R * p.L, s.stage + (size_t)ow * p.stage_stride, c1 < total ? c1 : total);
+    bulk_store_live(p, s.stage + (size_t)ow * p.stage_stride, a.obs + (size_t)(e0 + ow) * p.R * p.L);
     bulk_commit();
   }
 
@@ -1061,14 +1093,19 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         // terminal observation of a finished env: the whole image (staged rows + zero padding) to its term_obs row
         const size_t RL = (size_t)p.R * p.L;
         fence_async_smem();
-        bulk_copy_rows(p, s.stage + (size_t)t * p.stage_stride, s.zeros,
-                       a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[t] : (size_t)e) * RL);
+        float* trow = a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[t] : (size_t)e) * RL;
+        if (p.pad_persist || p.dead_hi > p.dead_lo) {
+          bulk_store_live(p, s.stage + (size_t)t * p.stage_stride, trow);
+          if (!p.pad_persist && p.zero_bytes > 0) bulk_store(reinterpret_cast<char*>(trow) + p.stage_stride * 4, s.zeros, (unsigned)p.zero_bytes);
+        } else {
+          bulk_copy_rows(p, s.stage + (size_t)t * p.stage_stride, s.zeros, trow);
+        }
         bulk_commit();
       }
     }
     const unsigned m = __ballot_sync(0xffffffffu, fin);
     if (fin) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
-    if (t == 0) { s.misc[1] = __popc(m); if (blockIdx.x == 0) atomicAdd(a.stats + 10, (double)E); }
+    if (t == 0) { s.misc[1] = __popc(m); if (blockIdx.x == 0) { atomicAdd(a.stats + 10, (double)E); if (a.term_count_next) *a.term_count_next = 0; } }
   }
   CHS_STAMP(9);
   __syncthreads();

@@ -44,6 +44,8 @@ struct KParams {
   int bulk_ok;           // observations leave through bulk (TMA) stores: R*L*4 and the staging stride are multiples of 16 B
   int zero_bytes;        // size of the shared zero block = R*L*4 - min(stage_stride*4, R*L*4)
   int pad_persist;       // rows >= D of an obs image are caller-owned zeros: chs_step does not write them (ChsParams.persistent_padding)
+  int dead_lo, dead_hi;  // columns [dead_lo, dead_hi) of every live obs row are caller-owned constant zeros (the unused neighbour
+                         // slots, BaseRLAviary.py:313-314): not rewritten by chs_step when persistent_padding is on; 0, 0 = none
   int early_ok;          // warp 0 may start its drone chain before the other warps finish staging (CHS_NO_EARLY=1 clears it)
   uint32_t seed_lo, seed_hi;
 };
@@ -74,6 +76,7 @@ template <typename T> struct KArgs {
   int term_mode;
   int* term_count;                   // mode 2: atomic row counter
   int* term_idx;                     // mode 2: env index of each compact row
+  int* term_count_next;              // mode 2, nullable: the counter the NEXT call will use; zeroed by this launch (ping-pong)
   const uint8_t* reset_mask;         // reset kernel only (nullable = all)
   int* done_list;                    // deferred reset (split mode): env ids finished this step (nullable = reset in the kernel)
   int* done_count;                   // number of entries, zeroed by drone_kernel

@@ -137,6 +137,45 @@ __device__ __forceinline__ void drone_cattle(const KParams& p, int g, int d, boo
   }
 }
 
+// The same work spread over C = 2^k lanes of one warp per (drone, env) item (lanes sub = 0..C-1 are consecutive): lane
+// `sub` takes cows sub, sub + C, ...; the minimum is combined with xor-shuffles, so EVERY lane of the warp has to call
+// this function the same number of times (`valid` = false: the lane only takes part in the shuffles).  min() is
+// order independent, so the result is bit for bit the serial one; with 100 cows the per-drone loop is the longest chain
+// of phase 2 otherwise (BASELINE config 3).
+template <typename T>
+__device__ __forceinline__ void drone_cattle_coop(const KParams& p, bool valid, int g, int d, int sub, int C, bool want_reward,
+                                                  const typename VT<T>::v4* s_dpos, const typename VT<T>::v2* s_cpos,
+                                                  typename VT<T>::v4* s_redB, float* s_stage) {
+  const int G = p.G;
+  T m2 = Mth<T>::inf();
+  if (valid) {
+    const auto me = s_dpos[d * G + g];
+    float* row = s_stage + (size_t)g * p.stage_stride + d * p.L;
+    const int cbase = (p.packing == CHS_PACK_MARL) ? 10 + 2 * 4 : 10 + 2 * CHS_MAX_DRONES;
+    const int nobs = (p.M < 16) ? p.M : 16;
+    const int jend = want_reward ? p.M : nobs;
+    const bool al8 = (p.L & 1) == 0;
+    for (int j = sub; j < jend; j += C) {
+      const auto c = s_cpos[j * G + g];
+      const T dx = c.x - me.x, dy = c.y - me.y;
+      if (j < nobs) {
+        const int col = cbase + 2 * j;
+        if (col + 1 < p.L) {
+          if (al8) *reinterpret_cast<float2*>(row + col) = make_float2((float)dx, (float)dy);
+          else { row[col] = (float)dx; row[col + 1] = (float)dy; }
+        } else if (col < p.L) { row[col] = (float)dx; }
+      }
+      m2 = Mth<T>::min(m2, dx * dx + dy * dy);
+    }
+  }
+  for (int o = C >> 1; o > 0; o >>= 1) {
+    const T other = __shfl_xor_sync(0xffffffffu, m2, o);
+    // fmin semantics: a NaN distance loses against a number on either side, like the serial loop
+    m2 = Mth<T>::min(m2, other);
+  }
+  if (valid && want_reward && sub == 0) reinterpret_cast<T*>(&s_redB[d * G + g])[0] = cattle_spacing<T>(Mth<T>::sqrt(m2));
+}
+
 // CattleAviary._computeTerminated (:422-492) and MARLCattleAviary._computeTerminated (:246-321); stateful
 // through the spacing clock (levels 0/1).  `ms` = minimum pairwise drone xy spacing, `cent` = centroid
 // distance, `eff` = effectiveness in percent, `clock_inc` = what one CALL adds to the clock: a hard-coded
