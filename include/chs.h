@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define CHS_ABI_VERSION 3
+#define CHS_ABI_VERSION 4
 #define CHS_MAX_DRONES 12   /* GLOBAL_MAX_NUM_DRONES, BaseAviary.py:112 */
 #define CHS_NUM_STATS 16
 #define CHS_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)   /* size of the static device array behind chs_step_static_scratch */
@@ -99,7 +99,12 @@ typedef struct ChsParams {
                                  2..11 (columns 14..33, BaseRLAviary.py:313-314 pads 2 active neighbours to 12 slots) are
                                  zeros that chs_reset_host writes and chs_step_host skips (fewer bytes across PCIe).
                                  0: every call rewrites the full image (the reference's _computeObs does, BaseRLAviary.py:334) */
-  int32_t reserved1;
+  int32_t marl_wrapper_quirks;/* MARL packing only, default 0.  1: reward / terminated / truncated are what the reference's RLlib wrapper
+                                 hands to RLlib (rllib_envs/marl_wrapper.py:104-117), not what env.step returned: the wrapper calls the
+                                 stateful per-agent functions a SECOND time for every agent still in its `agents` list (approach term
+                                 0, two more spacing-clock ticks and possibly another tally bump per agent), agents whose second-pass
+                                 `terminated` is set leave the list, and both "__all__" columns mean "the list is empty".  Slots of
+                                 agents that left the list read 0.  The list is part of the state (ChsStateView.active_agents) */
   uint64_t seed;              /* Philox key; streams are keyed by (seed, global env id, episode) */
 } ChsParams;
 
@@ -144,6 +149,11 @@ typedef struct ChsStateView {
   int32_t* tally;         /* [n]  CurriculumLearning.curriculum_success_tally */
   int32_t* spawn_idx;     /* [n]  BaseAviary.Cattle_Spawn_Index */
   int32_t* episode;       /* [n]  episodes started so far (Philox counter) */
+  int32_t* active_agents; /* [n]  RLlibMultiAgentWrapper.agents as a bit mask, bit i = "agent_i" (marl_wrapper.py:50,113); only
+                             maintained with ChsParams.marl_wrapper_quirks, rebuilt on the first step of every episode (:68-72) */
+  double* path_len;       /* [n][D]  BaseAviary.episode_drone_distances minus the spawn position it starts from (:683-688): the
+                             running 1.7 x xy path length of each drone (:1418-1426).  A NEGATIVE value marks an episode that has
+                             not stepped yet: its first step is measured from the origin (last_drones_pos is zeroed by reset, :317) */
 } ChsStateView;
 
 int chs_abi_version(void);
@@ -236,8 +246,16 @@ int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev);
 /* Episode statistics accumulated on device since the last reset of the accumulator:
  * float64 [CHS_NUM_STATS] = { episodes, sum return, sum length (control steps), terminated,
  * trunc altitude, trunc collision, trunc formation, trunc boundary, trunc time limit,
- * non-finite envs, env steps, 0... }.  Copies to stats_host (synchronous); `reset`!=0 zeroes the
- * accumulator afterwards.  This is the vector all-reduced over NCCL once per training iteration. */
+ * non-finite envs, env steps,
+ * [11] sum over finished episodes of the 1.7 x path length of all their drones (update_evaluation_metrics,
+ *      BaseAviary.py:1418-1426, first step measured from the origin like the reference),
+ * [12] sum over finished episodes of the herding effectiveness in percent at their last step
+ *      (evaluation_episode_trigger :1439-1450, utils/evaluation.py:100-138),
+ * [13] sum over ALL env-steps of the effectiveness in percent (the log's effectiveness_per_step; mean = [13] / [10]),
+ * [14] curriculum successes = increments of curriculum_success_tally, [15] level-ups
+ *      (utils/curriculum_learning.py:200-222), both summed over envs }.
+ * Copies to stats_host (synchronous); `reset`!=0 zeroes the accumulator afterwards.  This is the vector all-reduced over
+ * NCCL once per training iteration. */
 int chs_stats(ChsHandle* h, double* stats_host, int32_t reset);
 
 /* Launch-shape override after creation (bench autotuning): envs per CTA (1,2,4,8,16,32) and threads

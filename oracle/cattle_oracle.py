@@ -932,6 +932,29 @@ class OracleEnv:
         self.step_counter += 1
         return obs, rew, term, trunc
 
+    def step_rllib_wrapper(self, action, agents_mask):
+        """What the reference's `RLlibMultiAgentWrapper.step` hands to RLlib (rllib_envs/marl_wrapper.py:77-119): it steps
+        the env, DISCARDS the outputs and calls the stateful per-agent functions again, interleaved per agent, for the
+        agents still in its `agents` list (`agents_mask`, bit i = agent_i); agents whose second-pass `terminated` is set
+        leave the list.  Returns (obs, reward, terminated, truncated, new_mask); entries of unlisted agents are zero."""
+        obs1, _, _, _ = self.step_marl(action)
+        n = self.n_drones
+        obs = np.zeros_like(obs1)
+        rew = np.zeros(NMAX)
+        term = np.zeros(NMAX, dtype=bool)
+        trunc = np.zeros(NMAX, dtype=bool)
+        mask = int(agents_mask)
+        for i in range(n):
+            if not (mask >> i) & 1:
+                continue
+            obs[i] = obs1[i]                              # _computeObs is pure: same row as the step's
+            rew[i] = self.compute_reward_marl(i)
+            term[i] = self.compute_terminated_marl()
+            trunc[i] = self.compute_truncated_marl(i)
+            if term[i]:
+                mask &= ~(1 << i)
+        return obs, rew, term, trunc, mask
+
     # ---------------------------------------------------------------------------------------------
     # step  (BaseAviary.py:335-465)
     # ---------------------------------------------------------------------------------------------

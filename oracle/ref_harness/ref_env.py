@@ -309,3 +309,76 @@ def record_marl_rollout(env, actions, reset_first=True):
             quiet(env.reset)
         rows.append(row)
     return {k: np.stack([r[k] for r in rows]) for k in rows[0]}
+
+
+# ---- RLlib wrapper (rllib_envs/marl_wrapper.py) ---------------------------------------------------------
+def make_reference_wrapper(n_drones, n_cattle, ctrl_freq=30, pyb_freq=240, level=0, seed=0, spawn_table=None):
+    """Constructs the reference's `RLlibMultiAgentWrapper` through its own `__init__` (which builds the
+    `MARLCattleAviary` from `env_config`), with `ray.rllib.env.MultiAgentEnv` taken from the stand-in package and the
+    same harness-side pinning as `make_reference_marl_env` (drone count, spawn table, start level)."""
+    MARL, Physics, ActionType, m_mod = import_reference_marl()
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        with contextlib.redirect_stdout(io.StringIO()):
+            import gym_pybullet_drones.rllib_envs.marl_wrapper as w_mod
+    import yaml
+    random.seed(seed)
+    np.random.seed(seed)
+    orig_load = yaml.safe_load
+    orig_cl = m_mod.CurriculumLearning
+    if spawn_table is not None:
+        d = table_to_yaml_dict(np.asarray(spawn_table))
+        yaml.safe_load = lambda f: d
+    if level != 0:
+        m_mod.CurriculumLearning = lambda _lvl: orig_cl(level)
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = w_mod.RLlibMultiAgentWrapper(dict(num_drones=12, num_cattle=n_cattle, physics=Physics.DYN, pyb_freq=pyb_freq,
+                                                  ctrl_freq=ctrl_freq, act=ActionType.VEL))
+    finally:
+        yaml.safe_load = orig_load
+        m_mod.CurriculumLearning = orig_cl
+    w.env.MIN_NUM_DRONES = w.env.MAX_NUM_DRONES = n_drones
+    return w
+
+
+def _agent_mask(w):
+    return np.int32(sum(1 << int(a.split("_")[1]) for a in w.agents))
+
+
+def record_wrapper_rollout(w, actions, reset_first=True):
+    """Steps the reference WRAPPER (marl_wrapper.py:77-119) with `agent_<i>` action dicts for the agents still in its
+    `agents` list.  Outputs are (12,) arrays with zeros for agents that got no entry; `before_/after_active_agents` is the
+    wrapper's `agents` list as a bit mask.  An episode is restarted when the wrapper reports "__all__" or -- because its
+    "__all__" only ever follows terminations (:116-117) -- when any agent is truncated (`reset_after`)."""
+    if reset_first:
+        quiet(w.reset)
+    rows = []
+    for t in range(actions.shape[0]):
+        env = w.env
+        before = capture_state(env)
+        before["active_agents"] = _agent_mask(w)
+        n = env.NUM_DRONES
+        a = actions[t].astype(np.float32)
+        obs, rew, term, trunc, _ = quiet(w.step, {aid: a[int(aid.split("_")[1])] for aid in w.agents})
+        after = capture_state(env)
+        after["active_agents"] = _agent_mask(w)
+        L = env.observation_space.shape[0]
+        O = np.zeros((NMAX, L), dtype=np.float32)
+        R = np.zeros((NMAX,), dtype=np.float64)
+        T = np.zeros((NMAX,), dtype=np.uint8)
+        U = np.zeros((NMAX,), dtype=np.uint8)
+        for aid in obs:
+            i = int(aid.split("_")[1])
+            O[i], R[i], T[i], U[i] = obs[aid], rew[aid], bool(term[aid]), bool(trunc[aid])
+        row = {"action": a, "obs": O, "reward": R, "terminated": T, "truncated": U,
+               "term_all": np.uint8(bool(term["__all__"])), "trunc_all": np.uint8(bool(trunc["__all__"]))}
+        row.update({"before_" + k: v for k, v in before.items()})
+        row.update({"after_" + k: v for k, v in after.items()})
+        done = bool(term["__all__"]) or bool(U[:n].any())
+        row["reset_after"] = np.uint8(done)
+        if done:
+            quiet(w.reset)
+        rows.append(row)
+    return {k: np.stack([r[k] for r in rows]) for k in rows[0]}

@@ -8,13 +8,14 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("CHS_LIB", os.path.join(_HERE, "libchs.so"))   # CHS_LIB: build-variant experiments
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 MAX_DRONES = 12
 NUM_STATS = 16
 STATIC_SCRATCH_BYTES = 8 * 1024 * 1024
 
 STAT_NAMES = ("episodes", "sum_return", "sum_length", "terminated", "trunc_altitude", "trunc_collision",
-              "trunc_formation", "trunc_boundary", "trunc_time_limit", "non_finite", "env_steps")
+              "trunc_formation", "trunc_boundary", "trunc_time_limit", "non_finite", "env_steps", "sum_path_length",
+              "sum_final_effectiveness", "sum_step_effectiveness", "curriculum_successes", "level_ups")
 
 # every symbol include/chs.h declares (checked by tests/test_abi.py)
 SYMBOLS = ("chs_abi_version", "chs_last_error", "chs_create", "chs_destroy", "chs_get_dims", "chs_set_spawn_table",
@@ -30,7 +31,7 @@ class ChsParams(C.Structure):
                 ("packing", C.c_int32), ("precision", C.c_int32), ("auto_reset", C.c_int32),
                 ("aero_flags", C.c_int32), ("cattle_integrate", C.c_int32), ("env_id_offset", C.c_int32),
                 ("envs_per_block", C.c_int32), ("threads_per_block", C.c_int32), ("step_mode", C.c_int32),
-                ("persistent_padding", C.c_int32), ("reserved1", C.c_int32), ("seed", C.c_uint64)]
+                ("persistent_padding", C.c_int32), ("marl_wrapper_quirks", C.c_int32), ("seed", C.c_uint64)]
 
 
 class ChsDims(C.Structure):
@@ -43,11 +44,14 @@ _F64 = ("pos", "quat", "rpy", "vel", "ang_v", "rpy_rates", "last_rpm", "pid_ipos
         "cattle_pos", "cattle_vel", "prev_cent_dist", "spacing_clock", "ep_return")
 _I64 = ("step_counter",)
 _I32 = ("step_counter_A", "n_drones", "level", "tally", "spawn_idx", "episode")
+_I32_TAIL = ("active_agents",)  # appended to ChsStateView in ABI 4
+_F64_TAIL = ("path_len",)
 
 
 class ChsStateView(C.Structure):
     _fields_ = ([(n, C.POINTER(C.c_double)) for n in _F64] + [(n, C.POINTER(C.c_int64)) for n in _I64] +
-                [(n, C.POINTER(C.c_int32)) for n in _I32])
+                [(n, C.POINTER(C.c_int32)) for n in _I32] + [(n, C.POINTER(C.c_int32)) for n in _I32_TAIL] +
+                [(n, C.POINTER(C.c_double)) for n in _F64_TAIL])
 
 
 _lib = None

@@ -61,6 +61,7 @@ class BaseAviary:
         self.is_evaluating = False
         self.step_counter = 0
         self._device = self.sim.device
+        self._tl_seen, self._last_state = 0.0, None
         from .telemetry import EvaluationLog
         self._eval = EvaluationLog(self.sim, 0)
         self.eval_system = self._eval              # the reference's attribute name (BaseAviary.py:124)
@@ -70,8 +71,15 @@ class BaseAviary:
         """BaseAviary.reset (:280-331).  Like the reference, `seed` does not reseed the environment."""
         obs = self.sim.reset()
         self._refresh()
-        self._eval.on_reset()
+        self._eval.on_reset(self._last_state)
         return obs[0].cpu().numpy(), self._computeInfo()
+
+    def set_state(self, state):
+        """Checkpoint / test hook (no counterpart in the reference): injects a simulator state (the
+        fields of `CattleHerdingBatchedEnv.get_state`, leading dimension 1) as if `reset()` had produced it."""
+        self.sim.set_state(state)
+        self._refresh()
+        self._eval.on_reset(self._last_state)
 
     def step(self, action):
         """BaseAviary.step (:335-465)."""
@@ -81,11 +89,24 @@ class BaseAviary:
         obs, rew, term, trunc = self.sim.step(a.to(self._device))
         out = (obs[0].cpu().numpy(), float(rew[0].item()), bool(term[0].item()), bool(trunc[0].item()), self._computeInfo())
         self._refresh()
-        self._eval.on_step()                       # update_evaluation_metrics runs every step (BaseAviary.py:462)
-        # evaluation_episode_trigger: only an evaluating env whose episode hit the time limit (CattleAviary.py:545-550)
-        if self.is_evaluating and out[3] and self.step_counter / self.CTRL_FREQ > self.EPISODE_LEN_SEC:
-            self._eval.on_episode_end()
+        # evaluation_episode_trigger: only an evaluating env, only when the TIME LIMIT is what truncated the episode (the
+        # earlier causes return first, CattleAviary.py:509-542), decided on the pre-increment counter like every other time
+        # of the log, before this step's sample is appended, and once per _computeTruncated call: _computeReward (:315)
+        # and step (BaseAviary.py:460) each make one
+        hit = out[3] and self._time_limit_hit()
+        if self.is_evaluating and hit:
+            self._eval.on_episode_end(self._last_state)
+            self._eval.on_episode_end(self._last_state)
+        self._eval.on_step(self._last_state)       # update_evaluation_metrics runs every step (BaseAviary.py:462)
         return out
+
+    def _time_limit_hit(self):
+        """Did the simulator count a time-limit truncation since the last look?  (`chs_stats` slot 8: the kernel records the
+        first cause that fired, in the reference's order.)"""
+        count = float(self.sim.stats()[8])
+        hit = count > self._tl_seen
+        self._tl_seen = count
+        return hit
 
     def render(self, mode="human", close=False):
         """Text summary like BaseAviary.render (:469-494); there is no GUI."""
@@ -127,7 +148,7 @@ class BaseAviary:
         return np.hstack([s["cattle_pos"][0, j], [0, 0, 0, 1], [0, 0, 0], s["cattle_vel"][0, j], [0, 0, 0]])
 
     def _refresh(self):
-        s = self.sim.get_state()
+        s = self._last_state = self.sim.get_state()
         self.NUM_DRONES = int(s["n_drones"][0])
         self.step_counter = int(s["step_counter"][0])
 

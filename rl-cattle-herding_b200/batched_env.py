@@ -13,8 +13,8 @@ import torch
 from . import _lib
 from .enums import ACT_CODE, ACT_WIDTH
 
-STATE_F64 = _lib._F64
-STATE_INT = _lib._I64 + _lib._I32
+STATE_F64 = _lib._F64 + _lib._F64_TAIL
+STATE_INT = _lib._I64 + _lib._I32 + _lib._I32_TAIL
 
 
 def _ptr(t):
@@ -43,12 +43,16 @@ class CattleHerdingBatchedEnv:
     tensors `self.obs` / `self.terminal_obs` (and the pinned host mirrors) are owned by this object and are created
     zero-filled, so the simulator writes those rows at `reset()` only and never again: 3/4 of the bytes of an image
     at 3 drones.  Turn it off to have every step rewrite the full image.
+
+    `marl_wrapper_quirks` (MARL packing, default off): reward / flags are what the reference's RLlib wrapper reports --
+    the second invocation of the stateful per-agent functions (rllib_envs/marl_wrapper.py:104-117), see include/chs.h.
     """
 
     def __init__(self, num_envs, num_drones=3, num_cattle=20, pyb_freq=240, ctrl_freq=30, act="vel",
                  start_level=7, fixed_num_drones=0, obs_rows=None, auto_reset=True, precision="fp32",
                  spawn_table=None, device=None, env_id_offset=0, seed=0, envs_per_block=0, threads_per_block=0,
-                 packing="ctde", aero=0, cattle_integrate=False, step_mode="auto", persistent_padding=True):
+                 packing="ctde", aero=0, cattle_integrate=False, step_mode="auto", persistent_padding=True,
+                 marl_wrapper_quirks=False):
         if not torch.cuda.is_available():
             raise RuntimeError("CattleHerdingBatchedEnv needs a CUDA device (there is no CPU fallback)")
         self.lib = _lib.load()
@@ -71,6 +75,7 @@ class CattleHerdingBatchedEnv:
         p.auto_reset, p.env_id_offset, p.seed = int(bool(auto_reset)), int(env_id_offset), int(seed)
         p.envs_per_block, p.threads_per_block = int(envs_per_block), int(threads_per_block)
         p.persistent_padding = int(bool(persistent_padding))
+        p.marl_wrapper_quirks = int(bool(marl_wrapper_quirks))
         self.persistent_padding = bool(persistent_padding)
         self._h = C.c_void_p(0)
         _lib.check(self.lib.chs_create(C.byref(p), int(num_envs), self.device.index, C.byref(self._h)))
@@ -243,10 +248,10 @@ class CattleHerdingBatchedEnv:
         shp = {"pos": (n, D, 3), "quat": (n, D, 4), "rpy": (n, D, 3), "vel": (n, D, 3), "ang_v": (n, D, 3),
                "rpy_rates": (n, D, 3), "last_rpm": (n, D, 4), "pid_ipos": (n, D, 3), "pid_last_rpy": (n, D, 3),
                "pid_irpy": (n, D, 3), "cattle_pos": (n, M, 3), "cattle_vel": (n, M, 3), "prev_cent_dist": (n,),
-               "spacing_clock": (n,), "ep_return": (n,)}
+               "spacing_clock": (n,), "ep_return": (n,), "path_len": (n, D)}
         out = {k: np.zeros(s, dtype=np.float64) for k, s in shp.items()}
         out["step_counter"] = np.zeros((n,), dtype=np.int64)
-        for k in _lib._I32:
+        for k in _lib._I32 + _lib._I32_TAIL:
             out[k] = np.zeros((n,), dtype=np.int32)
         v = self._view(out)
         _lib.check(self.lib.chs_get_state(self._h, int(env0), int(n), C.byref(v)))

@@ -49,7 +49,7 @@ struct ChsHandle {
   int E, device;
   bool f64;
   size_t tsz;                 // sizeof(T)
-  void *drone, *rpm, *cpos, *cvel, *envf, *epret, *spawn;
+  void *drone, *rpm, *cpos, *cvel, *envf, *epret, *spawn, *path;
   int4 *envi, *envj;
   double* stats;
   double* tab;
@@ -192,6 +192,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   if (prm->start_level < 0 || prm->start_level >= k::NUM_LEVELS) return fail(CHS_ERR_INVALID, "start_level must be 0..7");
   if (prm->packing != CHS_PACK_CTDE && prm->packing != CHS_PACK_MARL) return fail(CHS_ERR_INVALID, "unknown packing %d", prm->packing);
   if (prm->aero_flags < 0 || prm->aero_flags > 7) return fail(CHS_ERR_INVALID, "aero_flags must be a combination of bits 0..2");
+  if (prm->marl_wrapper_quirks && prm->packing != CHS_PACK_MARL) return fail(CHS_ERR_INVALID, "marl_wrapper_quirks needs the MARL packing");
   if (prm->fixed_num_drones < 0 || prm->fixed_num_drones > prm->max_drones)
     return fail(CHS_ERR_INVALID, "fixed_num_drones must be 0..max_drones");
   int R = prm->obs_rows == 0 ? (prm->packing == CHS_PACK_MARL ? prm->max_drones : CHS_MAX_DRONES) : prm->obs_rows;
@@ -251,6 +252,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   h->knob_no_direct = getenv("CHS_NO_DIRECT") != nullptr;
   kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
+  kp.wrapper_quirks = (prm->marl_wrapper_quirks && prm->packing == CHS_PACK_MARL) ? 1 : 0;
   kp.aero_flags = prm->aero_flags;
   kp.act4_ok = (A == 4) ? 1 : 0;
   kp.seed_lo = (uint32_t)(prm->seed & 0xffffffffu); kp.seed_hi = (uint32_t)(prm->seed >> 32);
@@ -267,6 +269,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   ALLOC0(h->cvel, M * E * 2 * ts);
   ALLOC0(h->envf, E * sizeof(double2));
   ALLOC0(h->epret, E * sizeof(double));
+  ALLOC0(h->path, D * E * ts);
   ALLOC0(h->envi, E * sizeof(int4));
   ALLOC0(h->envj, E * sizeof(int4));
   ALLOC0(h->stats, (size_t)CHS_STAT_ROWS * CHS_NUM_STATS * sizeof(double));
@@ -321,7 +324,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
 extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
-  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count, h->amask,
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->path, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count, h->amask,
                   h->d_actions, h->d_obs, h->d_small, h->d_termobs, h->d_mask};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_small) cudaFreeHost(h->h_small);
@@ -419,7 +422,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.p = h->kp;
   a.drone = (typename VT<T>::v4*)h->drone; a.rpm = (typename VT<T>::v4*)h->rpm;
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
-  a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret;
+  a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret; a.path = (T*)h->path;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats; a.tab = h->tab;
   a.amask = (h->amask_ok && !h->kp.cattle_integrate) ? h->amask : nullptr;
   a.own2 = (typename VT<T>::v4*)h->own2; a.pos0 = (const typename VT<T>::v4*)h->pos0;
@@ -470,7 +473,7 @@ template <> void launch_step_variant<float>(ChsHandle* h, const KArgs<float>& a,
   const bool big = (h->reg_variant == 2 && h->threads <= 256) || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
   const bool marl = h->kp.packing == CHS_PACK_MARL, split = a.p.split != 0;
   // lean build unless a runtime-checked feature is in use
-  const bool full = a.p.aero_flags || a.p.cattle_integrate || !a.p.cp_ok || !a.p.bulk_ok || a.dbg_clock || h->knob_full;
+  const bool full = a.p.aero_flags || a.p.cattle_integrate || a.p.wrapper_quirks || !a.p.cp_ok || !a.p.bulk_ok || a.dbg_clock || h->knob_full;
   if (full) { if (big) CHS_LAUNCH(float, 256, 4, true); else CHS_LAUNCH(float, 512, 1, true); }
   else      { if (big) CHS_LAUNCH(float, 256, 4, false); else CHS_LAUNCH(float, 512, 1, false); }
 }

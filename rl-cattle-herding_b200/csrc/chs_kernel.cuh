@@ -15,6 +15,9 @@
 //   phase 4  coalesced copy of the staged observation rows (and zero padding) to the obs tensor
 //   phase 5  (only CTAs with a finished env, auto_reset) reset those envs in place and emit their first obs
 #pragma once
+#ifndef CHS_EXP
+#define CHS_EXP 0
+#endif
 #include "chs_drone.cuh"
 #include "chs_flock.cuh"
 #include "chs_task.cuh"
@@ -150,6 +153,16 @@ __device__ __forceinline__ int draw_num_drones(const KParams& p, int gid, int ep
   return n > p.D ? p.D : n;
 }
 
+// update_evaluation_metrics (BaseAviary.py:1418-1426): the running distance of a drone grows by 1.7 x the xy length of
+// this step; `acc` < 0 marks an episode that has not stepped yet, whose first step is measured from the origin
+// (last_drones_pos is zeroed by reset, :317).
+template <typename T>
+__device__ __forceinline__ T path_advance(T acc, T bx, T by, T ax, T ay) {
+  const bool fresh = acc < T(0);
+  const T dx = ax - (fresh ? T(0) : bx), dy = ay - (fresh ? T(0) : by);
+  return (fresh ? T(0) : acc) + Mth<T>::sqrt(dx * dx + dy * dy) * T(1.7);
+}
+
 // Phase 5 / reset kernel body: in-place reset of the envs listed in s.dlist[0..nd) and emission of their
 // first observation (BaseAviary.reset :280-331, _housekeeping :547-637, initialize_drone_positions
 // :251-277).  PID state, prev_cent_dist, the spacing clock and the curriculum survive.
@@ -199,6 +212,7 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
     }
     store_drone<T>(a, d, e, ds);
     a.rpm[(size_t)d * E + e] = mk4<T>(0, 0, 0, 0);
+    a.path[(size_t)d * E + e] = T(-1);
     s.dpos[d * G + g] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], T(0));
     if (d == 0) s.n[g] = n;
   }
@@ -366,6 +380,7 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
     base[F_F * st] = mk4<T>(pid.f.x, pid.f.y, pid.f.z, 0);
     base[F_G * st] = mk4<T>(pid.g.x, pid.g.y, pid.g.z, 0);
     a.rpm[(size_t)d * E + e] = mk4<T>(0, 0, 0, 0);
+    a.path[(size_t)d * E + e] = T(-1);
   }
   if (a.obs == nullptr || !(parts & RESET_OBS)) return;
   // two nearest other drones of drone `lane` (strict '<' keeps index order on ties, like drone_neighbors)
@@ -497,6 +512,8 @@ __global__ void __launch_bounds__(256) drone_kernel(const KArgs<T> a) {
   const T pyb_dt = T(1.0) / T(p.ctrl_freq * p.K);
   DroneState<T> ds;
   load_drone<T>(a, d, e, ds);
+  const T path0 = a.path[(size_t)d * E + e];
+  const T bx = ds.p[0], by = ds.p[1];
   float act[4] = {0.f, 0.f, 0.f, 0.f};
   const float* ap = a.actions + ((size_t)e * D + d) * p.A;
   if (p.A == 4 && p.act4_ok) {
@@ -521,6 +538,7 @@ __global__ void __launch_bounds__(256) drone_kernel(const KArgs<T> a) {
   store_drone<T>(a, d, e, ds);
   a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
   a.own2[(size_t)d * E + e] = mk4<T>(ds.av[0], ds.av[1], ds.av[2], ds.rpy[2]);
+  a.path[(size_t)d * E + e] = path_advance<T>(path0, bx, by, ds.p[0], ds.p[1]);
 }
 
 // Two register budgets are compiled: MINB = 1 (up to 128 registers per thread, shortest dependent chains, for
@@ -564,16 +582,18 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   DroneState<T> ds0;
   float act0[4] = {0.f, 0.f, 0.f, 0.f};
   typename VT<T>::v4 sp0 = mk4<T>(0, 0, 0, 0), sp1 = sp0, sp2 = sp0;     // split mode: fields A, C and the own2 row
+  T path0 = T(0);                                                        // running path length of the first drone item
   const bool have0 = (t < ndt) && (t < DG) && (e0 + (t & (G - 1)) < E);
   if constexpr (SPLIT) {
     if (have0) {
       const int g = t & (G - 1), d = t >> lg, e = e0 + g;
       const size_t st = (size_t)D * E, o = (size_t)d * E + e;
-      sp0 = a.drone[F_A * st + o]; sp1 = a.drone[F_C * st + o]; sp2 = a.own2[o];
+      sp0 = a.drone[F_A * st + o]; sp1 = a.drone[F_C * st + o]; sp2 = a.own2[o]; path0 = a.path[o];
     }
   } else if (have0) {
     const int g = t & (G - 1), d = t >> lg, e = e0 + g;
     load_drone<T>(a, d, e, ds0);
+    path0 = a.path[(size_t)d * E + e];
     const float* ap = a.actions + ((size_t)e * D + d) * p.A;
     if (p.A == 4 && p.act4_ok) {
       const float4 v = *reinterpret_cast<const float4*>(ap);
@@ -683,11 +703,12 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         const int g = it & (G - 1), d = it >> lg, e = e0 + g;
         if (e < E && d < s.n[g]) {
           typename VT<T>::v4 A = sp0, C = sp1, O = sp2;
+          T pl = path0;
           if (it != t) {
             const size_t st = (size_t)D * E, o = (size_t)d * E + e;
-            A = a.drone[F_A * st + o]; C = a.drone[F_C * st + o]; O = a.own2[o];
+            A = a.drone[F_A * st + o]; C = a.drone[F_C * st + o]; O = a.own2[o]; pl = a.path[o];
           }
-          s.dpos[it] = mk4<T>(A.x, A.y, A.z, T(0));
+          s.dpos[it] = mk4<T>(A.x, A.y, A.z, pl);         // .w: the drone's running path length (phase 3 sums it at episode end)
           float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
           if ((p.L & 1) == 0) {
             float2* r2 = reinterpret_cast<float2*>(row);
@@ -705,21 +726,25 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   } else if (t < ndt) {
     DroneState<T> held;            // early mode: the one item of this thread, parked until the staging area is ready
     int held_it = -1;
+    T held_pl = T(0);
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       if (e < E && d < s.n[g]) {
         DroneState<T> ds;
         float act[4];
+        T pl = path0;
         if (it == t) {
           ds = ds0;
 #pragma unroll
           for (int i = 0; i < 4; ++i) act[i] = act0[i];
         } else {
           load_drone<T>(a, d, e, ds);
+          pl = a.path[(size_t)d * E + e];
           const float* ap = a.actions + ((size_t)e * D + d) * p.A;
 #pragma unroll
           for (int i = 0; i < 4; ++i) act[i] = (i < p.A) ? ap[i] : 0.f;
         }
+        const T bx = ds.p[0], by = ds.p[1];
         T rpm[4];
         action_to_rpm<T>(p, ds, act, ctrl_dt, rpm);
         CHS_STAMP(16);
@@ -736,8 +761,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         CHS_STAMP(17);
         store_drone<T>(a, d, e, ds);
         a.rpm[(size_t)d * E + e] = mk4<T>(rpm[0], rpm[1], rpm[2], rpm[3]);
-        if (early) { held = ds; held_it = it; continue; }      // DG <= 32: one item per thread
-        s.dpos[it] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], T(0));
+        pl = path_advance<T>(pl, bx, by, ds.p[0], ds.p[1]);
+        a.path[(size_t)d * E + e] = pl;
+        if (early) { held = ds; held_it = it; held_pl = pl; continue; }      // DG <= 32: one item per thread
+        s.dpos[it] = mk4<T>(ds.p[0], ds.p[1], ds.p[2], pl);    // .w: running path length, summed by phase 3 at episode end
         // own-state part of the obs row (BaseRLAviary.py:286-297): z, rpy, vel, ang_v
         float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
         row[0] = (float)ds.p[2];
@@ -750,7 +777,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");     // the staging warps arrived here long ago
       if (held_it >= 0) {
         const int g = held_it & (G - 1), d = held_it >> lg;
-        s.dpos[held_it] = mk4<T>(held.p[0], held.p[1], held.p[2], T(0));
+        s.dpos[held_it] = mk4<T>(held.p[0], held.p[1], held.p[2], held_pl);
         float* row = s.stage + (size_t)g * p.stage_stride + d * p.L;
         row[0] = (float)held.p[2];
 #pragma unroll
@@ -823,10 +850,40 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       const int n = s.n[g];
       if (e < E && d < n)
         drone_neighbors<T>(p, s.ctab, g, d, n, s.level[g], true, s.dpos, s.redA, s.redB, s.stage,
-                           a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr);
+                           a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr,
+                           (FULL && a.dbg_clock && t == 0) ? a.dbg_clock + (size_t)blockIdx.x * 32 + 24 : nullptr);
     }
   }
   CHS_STAMP(19);
+#if CHS_EXP & 1
+  // Warp roles of phase 2: the drone warps rank their neighbours and nothing else (they are the critical path of the CTA: they
+  // come out of the serial drone chain last); of the other warps the first `cw` take the cattle pieces of the observation
+  // (lane-cooperative, shuffles inside a warp), the rest the per-cow herd update and the winding numbers.  A CTA without
+  // two spare warps keeps everything on all threads.
+  const int spare_w = (nt - ndt) >> 5;
+  const bool roles = (ndt < nt) && spare_w >= 2;
+  const int cw = roles ? (spare_w >= 4 ? spare_w >> 2 : 1) : 0;
+  {
+    const int c0 = roles ? ndt : 0, cn = roles ? (cw << 5) : nt;         // coop threads [c0, c0 + cn)
+    const int tb = roles ? t - c0 : ((t >= ((nt >> 1) & ~31)) ? t - ((nt >> 1) & ~31) : t + nt - ((nt >> 1) & ~31));
+    if (tb >= 0 && tb < cn) {
+      int lc;
+      if (roles) { lc = 0; while (lc < 3 && ((DG << lc) % cn) != 0) ++lc; }     // fewest lanes per item that fill every round
+      else { lc = 3; while (lc > 0 && (DG << lc) > cn) --lc; }
+      const int C = 1 << lc, items = DG << lc;
+      for (int base = 0; base < items; base += cn) {
+        const int idx = base + tb, it = idx >> lc, sub = idx & (C - 1);
+        const int g = it & (G - 1), d = it >> lg;
+        const bool valid = idx < items && e0 + g < E && d < s.n[g];
+        drone_cattle_coop<T>(p, valid, g, d, sub, C, true, s.dpos, s.cpos, s.redB, s.stage);
+      }
+    }
+  }
+  CHS_STAMP(20);
+  const int pw0 = roles ? ndt + (cw << 5) : ((ndt < nt) ? ndt : 0);
+  const int pnw = nt - pw0;
+  const int pw = t - pw0;               // < 0 on the warps with another role
+#else
   {
     // cattle pieces: C lanes per (drone, env) item, as many as the CTA has threads for (up to 8), on threads half a CTA away
     // from the drone warps; every thread runs the same number of rounds (the lanes of an item meet in shuffles)
@@ -848,6 +905,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   const int pw0 = (ndt < nt) ? ndt : 0;
   const int pnw = nt - pw0;
   const int pw = t - pw0;               // < 0 on the drone warps when they are exempt
+#endif
   if (!FULL || !p.cattle_integrate) {
     if (pw >= 0) for (int it = pw; it < nact * M; it += pnw) {
       const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
@@ -889,7 +947,8 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     const int4 ei = pre_i;
     bool st_term = false, st_trunc = false, st_bad = false, done_env = false;
     int st_cause = -1, sc = 0, scA = 0, nn = 0, row = 0;
-    double epret = 0;
+    int st_herded = 0, st_succ = 0, st_lvup = 0;      // telemetry: cows inside the drone polygon, curriculum successes / level-ups
+    double epret = 0, st_path = 0;
     if (active) {
       const int n = s.n[t];
       int level = ej.x;
@@ -912,6 +971,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         isolated = isolated || (B.y > T(k::MAX_FORMATION_DISTANCE));
         alt_bad = alt_bad || (B.z != T(0));
         dcx += (double)P.x; dcy += (double)P.y;
+        st_path += (double)P.w;
       }
       CHS_STAMP(14);
       const double inv_n = s.ctab[CHS_TAB_INV_N + n];
@@ -943,9 +1003,9 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         // first _computeTerminated call, inside _computeReward (:314): only its side effects survive
         const bool term1 = compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, 1.0 / 240.0);
         if (term1) {   // CurriculumLearning.evaluate_curriculum_results (curriculum_learning.py:200-222)
-          ej.y += 1;
+          ej.y += 1; st_succ = 1;
           if (ej.y >= (int)s.ctab[level_in * k::C_NCOLS + k::C_REQ_TALLY]) {
-            ej.y = 0;
+            ej.y = 0; st_lvup = 1;
             level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
           }
         }
@@ -974,7 +1034,8 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         uint8_t* tf = a.terminated + (size_t)e * (D + 1);
         uint8_t* uf = a.truncated + (size_t)e * (D + 1);
         bool all_term = true, all_trunc = true;
-        for (int d = 0; d < n; ++d) {
+        // one _computeReward(d) call (MARLCattleAviary.py:110-178), state effects included
+        auto agent_reward = [&](int d, bool& own_trunc) -> double {
           const auto A = s.redA[d * G + t];
           const auto B = s.redB[d * G + t];
           T s1 = A.x, s2 = A.y, c1 = A.z, c2 = A.w;
@@ -991,26 +1052,34 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
           r += approach * s.ctab[level * k::C_NCOLS + k::C_W_APPROACH];
           r += eff_frac * s.ctab[level * k::C_NCOLS + k::C_W_EFF];
           r += (double)B.x * s.ctab[level * k::C_NCOLS + k::C_W_C2D];
-          const bool own_trunc = (B.z != T(0)) || ((double)B.y < k::COLLISION_THRESHOLD) ||
-                                 (B.y > T(k::MAX_FORMATION_DISTANCE)) || shared_trunc;
+          own_trunc = (B.z != T(0)) || ((double)B.y < k::COLLISION_THRESHOLD) ||
+                      (B.y > T(k::MAX_FORMATION_DISTANCE)) || shared_trunc;
           if (compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, clk)) {
             const auto P = s.dpos[d * G + t];
             const double hx = cc.x - (double)P.x, hy = cc.y - (double)P.y;
             r += marl_end_of_episode(s.ctab, level, n, (double)B.y, (double)B.w, cent, eff, sqrt(hx * hx + hy * hy));
-            ej.y += 1;
+            ej.y += 1; st_succ += 1;
             if (ej.y >= (int)s.ctab[level * k::C_NCOLS + k::C_REQ_TALLY]) {
-              ej.y = 0;
+              ej.y = 0; st_lvup += 1;
               level = (level + 1 >= k::NUM_LEVELS) ? k::NUM_LEVELS - 1 : level + 1;
             }
           } else if (own_trunc) {
             r -= 50.0;
           }
+          return r;
+        };
+        for (int d = 0; d < n; ++d) {
+          bool own_trunc;
+          const double r = agent_reward(d, own_trunc);
           rw[d] = (float)r;
           r_global += r;
           uf[d] = own_trunc ? 1 : 0;
           all_trunc = all_trunc && own_trunc;
-          if (d == 0) cause = (B.z != T(0)) ? 0 : ((double)B.y < k::COLLISION_THRESHOLD) ? 1
-                              : (B.y > T(k::MAX_FORMATION_DISTANCE)) ? 2 : (cent > k::MISSION_BOUNDARY) ? 3 : 4;
+          if (d == 0) {
+            const auto B = s.redB[t];
+            cause = (B.z != T(0)) ? 0 : ((double)B.y < k::COLLISION_THRESHOLD) ? 1
+                    : (B.y > T(k::MAX_FORMATION_DISTANCE)) ? 2 : (cent > k::MISSION_BOUNDARY) ? 3 : 4;
+          }
         }
         for (int d = 0; d < n; ++d) {
           const bool td = compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, clk);
@@ -1019,12 +1088,34 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         }
         for (int d = n; d < D; ++d) { rw[d] = 0.f; tf[d] = 0; uf[d] = 0; }
         term = all_term; trunc = all_trunc;          // the "__all__" entries (:428,430)
+        if (FULL && p.wrapper_quirks) {
+          // Opt-in bug compatibility with the reference's RLlib wrapper (rllib_envs/marl_wrapper.py:104-110): after
+          // env.step it DISCARDS the step's outputs and calls the stateful _computeReward / _computeTerminated /
+          // _computeTruncated once more for every agent still in its `agents` list, interleaved per agent -- the approach
+          // term is then always 0 (prev_cent_dists was refreshed by the step), the spacing clock advances two more ticks
+          // per agent and a success bumps the tally again.  Agents whose second-pass `terminated` is set leave the list
+          // (:113); both "__all__" flags mean "the list is empty" (:116-117).  The list lives in envj.w as a bit mask and
+          // is rebuilt on the first step of an episode (the wrapper's reset, :68-72).
+          unsigned act = (ei.y == 0) ? 0xffffffffu : (unsigned)ej.w;
+          act &= (n >= 32) ? 0xffffffffu : ((1u << n) - 1u);
+          for (int d = 0; d < n; ++d) {
+            if (!((act >> d) & 1u)) { rw[d] = 0.f; tf[d] = 0; uf[d] = 0; continue; }
+            bool own_trunc;
+            rw[d] = (float)agent_reward(d, own_trunc);
+            const bool td = compute_terminated<double>(s.ctab, level, msd, cent, eff, ef.y, clk);
+            tf[d] = td ? 1 : 0; uf[d] = own_trunc ? 1 : 0;
+            if (td) act &= ~(1u << d);
+          }
+          ej.w = (int)act;
+          term = trunc = (act == 0u);
+        }
         tf[D] = term ? 1 : 0; uf[D] = trunc ? 1 : 0;
         if (!trunc) cause = -1;
       }
       ej.x = level;
       CHS_STAMP(8);
       if (a.dbg_herded) a.dbg_herded[e] = herded;
+      st_herded = herded;
       epret = pre_ret + r_global;
       sc = ei.x + sc_inc; scA = ei.y + 1; nn = n; row = ei.w;
       fin = term || trunc;
@@ -1044,7 +1135,20 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         atomicAdd(srow + 2, (double)scA);
         if (st_term) atomicAdd(srow + 3, 1.0);
         if (st_trunc && st_cause >= 0) atomicAdd(srow + 4 + st_cause, 1.0);
+        // evaluation telemetry of the finished episode (update_evaluation_metrics / evaluation_episode_trigger,
+        // BaseAviary.py:1406-1450): 1.7 x path length summed over its drones, effectiveness in percent at its last step
+        atomicAdd(srow + 11, st_path);
+        if (st_herded) atomicAdd(srow + 12, (double)st_herded * (100.0 * s.ctab[CHS_TAB_INV_M]));
       }
+      // curriculum_success_tally increments and level-ups (curriculum_learning.py:200-222), summed over envs
+      if (st_succ) atomicAdd(srow + 14, (double)st_succ);
+      if (st_lvup) atomicAdd(srow + 15, (double)st_lvup);
+    }
+    {
+      // per-step effectiveness (effectiveness_per_step of the reference's log), summed over the CTA's envs: one reduction
+      // and one RED per CTA
+      const int hsum = __reduce_add_sync(0xffffffffu, st_herded);
+      if (t == 0 && hsum) atomicAdd(a.stats + (size_t)(blockIdx.x & (CHS_STAT_ROWS - 1)) * CHS_NUM_STATS + 13, (double)hsum * (100.0 * s.ctab[CHS_TAB_INV_M]));
     }
     {
       const unsigned full = 0xffffffffu, lt = (1u << t) - 1u;

@@ -11,10 +11,13 @@
 //   cpos    v2 [M][E]      cattle xy (z is the constant 0.1; cattle never move in DYN)
 //   cvel    v2 [M][E]      cattle xy velocity (z = 0)
 //   envi  int4 [E]         step_counter, step_counter_A, n_drones, spawn_idx
-//   envj  int4 [E]         level, tally, episode, reserved
+//   envj  int4 [E]         level, tally, episode, active-agent bit mask of the RLlib wrapper (marl_wrapper_quirks only)
 //   envf double2 [E]       prev_cent_dist (NaN = None), spacing_clock -- float64 in BOTH builds: the approach
 //                          reward multiplies a difference of two ~10 m centroid distances by 5*ctrl_freq/2.5
 //   epret double [E]       running episode return (telemetry)
+//   path     T [D][E]      1.7 x xy path length of the running episode per drone (update_evaluation_metrics,
+//                          BaseAviary.py:1406-1435); negative = no step since the reset (the first step of an episode is
+//                          measured from the origin: last_drones_pos is zeroed by reset, :317)
 #pragma once
 #include "chs_math.cuh"
 #include "../../include/chs.h"
@@ -46,6 +49,7 @@ struct KParams {
   int pad_persist;       // rows >= D of an obs image are caller-owned zeros: chs_step does not write them (ChsParams.persistent_padding)
   int dead_lo, dead_hi;  // columns [dead_lo, dead_hi) of every live obs row are caller-owned constant zeros (the unused neighbour
                          // slots, BaseRLAviary.py:313-314): not rewritten by chs_step when persistent_padding is on; 0, 0 = none
+  int wrapper_quirks;    // MARL packing: outputs are those of the reference RLlib wrapper's second invocation (ChsParams.marl_wrapper_quirks)
   int early_ok;          // warp 0 may start its drone chain before the other warps finish staging (CHS_NO_EARLY=1 clears it)
   uint32_t seed_lo, seed_hi;
 };
@@ -62,6 +66,7 @@ template <typename T> struct KArgs {
   int4* envj;
   double2* envf;
   double* epret;
+  T* path;                           // [D][E] running 1.7 x path length per drone (BaseAviary.py:1424), < 0 = fresh episode
   const typename VT<T>::v2* spawn;   // [n_sims][spawn_stride]
   const unsigned* amask;             // nullable [n_sims][M][ceil(M/32)]: alpha-term in-range masks per spawn row (chs_flock.cuh)
   double* stats;                     // [CHS_STAT_ROWS][CHS_NUM_STATS], row = CTA index mod CHS_STAT_ROWS

@@ -60,7 +60,8 @@ template <typename T> __device__ __forceinline__ T cattle_spacing(T r) {
 template <typename T>
 __device__ __forceinline__ void drone_neighbors(const KParams& p, const double* ct, int g, int d, int n, int level, bool want_reward,
                                                 const typename VT<T>::v4* s_dpos, typename VT<T>::v4* s_redA,
-                                                typename VT<T>::v4* s_redB, float* s_stage, int* dbg_nb /* nullable: [2] */) {
+                                                typename VT<T>::v4* s_redB, float* s_stage, int* dbg_nb /* nullable: [2] */,
+                                                long long* clk = nullptr /* profiling: three clock64() stamps */) {
   const int G = p.G;
   const auto me = s_dpos[d * G + g];
   // two nearest other drones; strict '<' keeps index order on ties (stable sort, :310-311);
@@ -75,6 +76,7 @@ __device__ __forceinline__ void drone_neighbors(const KParams& p, const double* 
     if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
     else if (dist < d2) { d2 = dist; j2 = j; }
   }
+  if (clk) clk[0] = clock64();
   float* row = s_stage + (size_t)g * p.stage_stride + d * p.L;
   const int nb_slots = (p.L - 10) / 2;       // row truncated to L (BaseRLAviary.py:336-340)
   const bool al8 = (p.L & 1) == 0;
@@ -89,6 +91,7 @@ __device__ __forceinline__ void drone_neighbors(const KParams& p, const double* 
     else { row[12] = (float)(o.x - me.x); row[13] = (float)(o.y - me.y); }
   }
   if (dbg_nb) { dbg_nb[0] = j1; dbg_nb[1] = j2; }
+  if (clk) clk[1] = clock64();
   if (want_reward) {
     const T desired = curr<T>(ct, level, k::C_DESIRED), tolf = curr<T>(ct, level, k::C_TOL);
     s_redA[d * G + g] = mk4<T>(simple_spacing<T>(d1, desired, tolf), simple_spacing<T>(d2, desired, tolf),
@@ -98,6 +101,7 @@ __device__ __forceinline__ void drone_neighbors(const KParams& p, const double* 
     rb[2] = (Mth<T>::abs(me.z - T(k::TARGET_ALT)) > T(k::MAX_ALT_ERROR)) ? T(1) : T(0);
     rb[3] = d2;
   }
+  if (clk) clk[2] = clock64();
 }
 
 // cattle: relative xy of cows 0..15 into the obs row, minimum distance over ALL cows for the reward

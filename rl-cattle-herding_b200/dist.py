@@ -55,14 +55,35 @@ def summarize(stats):
     d = dict(zip(STAT_NAMES, np.asarray(stats, dtype=np.float64)[: len(STAT_NAMES)].tolist()))
     ep = max(1.0, d["episodes"])
     d["mean_return"], d["mean_length"] = d["sum_return"] / ep, d["sum_length"] / ep
+    # evaluation telemetry (utils/evaluation.py's per-episode / per-step quantities, averaged over the whole job)
+    d["mean_path_length"], d["mean_final_effectiveness"] = d["sum_path_length"] / ep, d["sum_final_effectiveness"] / ep
+    d["mean_step_effectiveness"] = d["sum_step_effectiveness"] / max(1.0, d["env_steps"])
     return d
 
 
 def gather_observations(obs, group=None):
     """Optional, for a single-process learner (SB3): all-gather of each rank's obs shard along the env axis.
-    Not part of the env-step metric."""
+    Not part of the env-step metric.  Shards may differ by one env (`shard_range` with total % world != 0): the shard
+    sizes are exchanged first and short shards are padded for the collective, then trimmed."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return obs
-    parts = [torch.empty_like(obs) for _ in range(dist.get_world_size(group))]
-    dist.all_gather(parts, obs.contiguous(), group=group)
-    return torch.cat(parts, dim=0)
+    ws = dist.get_world_size(group)
+    n = torch.tensor([obs.shape[0]], dtype=torch.int64, device=obs.device)
+    sizes = [torch.zeros_like(n) for _ in range(ws)]
+    dist.all_gather(sizes, n, group=group)
+    sizes = [int(x.item()) for x in sizes]
+    top = max(sizes)
+    mine = obs.contiguous()
+    if mine.shape[0] < top:
+        mine = torch.cat([mine, mine.new_zeros((top - mine.shape[0],) + tuple(mine.shape[1:]))], dim=0)
+    parts = [torch.empty_like(mine) for _ in range(ws)]
+    dist.all_gather(parts, mine, group=group)
+    return torch.cat([p[:k] for p, k in zip(parts, sizes)], dim=0)
+
+
+def require_even_shards(total_envs, world_size):
+    """Per-GPU learners run the same number of minibatches on every rank (one gradient all-reduce each, `ppo.update`):
+    shards of different size would leave a rank waiting in a collective the others never enter."""
+    if int(total_envs) % int(world_size) != 0:
+        raise ValueError(f"total envs ({total_envs}) must be a multiple of the number of ranks ({world_size}) for the "
+                         "per-GPU learners; the env-step path itself (make_sharded_env) takes uneven shards")

@@ -5,10 +5,13 @@
   `reset() -> ({i: obs_i}, {"__all__": {}})`, `step(action (N, A)) -> obs, reward, terminated, truncated, info`
   dicts keyed by drone index, the flag dicts carrying "__all__".
 * `RLlibMultiAgentWrapper` -- the `agent_<i>` keyed wrapper of `rllib_envs/marl_wrapper.py:8-125`
-  (`possible_agents`, `agents`, per-agent spaces, finished agents leave `agents`).  One deliberate difference:
-  the reference wrapper discards what `env.step` returned and calls the stateful `_computeReward / _computeTerminated
-  / _computeTruncated` a second time (marl_wrapper.py:104-110), which advances the spacing clock and the curriculum
-  tally twice per step; this wrapper hands out the outputs of the step itself.
+  (`possible_agents`, `agents`, per-agent spaces, finished agents leave `agents`).  The reference wrapper discards
+  what `env.step` returned and calls the stateful `_computeReward / _computeTerminated / _computeTruncated` a second
+  time (marl_wrapper.py:104-110), which advances the spacing clock and the curriculum tally twice per step and makes
+  the approach term always zero.  By default this wrapper hands out the outputs of the step itself;
+  `env_config["reference_wrapper_quirks"] = True` reproduces the reference wrapper bug for bug (the second invocation
+  runs inside the step kernel, `ChsParams.marl_wrapper_quirks`; pinned by tests/golden/wrapper/, recorded through the
+  reference's wrapper).
 * `GpuMARLBatchedEnv`      -- E environments at once, arrays in / arrays out (the per-drone dicts as `(E, D)` arrays).
 
 All arithmetic runs in `libchs.so`; there is no CPU path.
@@ -55,7 +58,7 @@ class MARLCattleAviary:
     def __init__(self, drone_model=DroneModel.CF2X, num_drones=2, num_cattle=1, neighbourhood_radius=np.inf,
                  initial_xyzs=None, initial_rpys=None, physics=Physics.DYN, pyb_freq=240, ctrl_freq=60, gui=False,
                  record=False, obs=ObservationType.COKIN, act=ActionType.VEL, seed=0, spawn_table=None, device=None,
-                 precision="fp32", fixed_num_drones=0, curriculum_level=0):
+                 precision="fp32", fixed_num_drones=0, curriculum_level=0, wrapper_quirks=False):
         if drone_model != DroneModel.CF2X:
             raise ValueError("only DroneModel.CF2X is implemented")
         if physics != Physics.DYN:
@@ -68,7 +71,9 @@ class MARLCattleAviary:
         self.sim = GpuMARLBatchedEnv(1, num_drones=num_drones, num_cattle=num_cattle, pyb_freq=pyb_freq,
                                      ctrl_freq=ctrl_freq, act=act, start_level=int(curriculum_level),
                                      fixed_num_drones=fixed_num_drones, auto_reset=False, precision=precision,
-                                     spawn_table=spawn_table, device=device, seed=seed)
+                                     spawn_table=spawn_table, device=device, seed=seed,
+                                     marl_wrapper_quirks=bool(wrapper_quirks))
+        self.wrapper_quirks = bool(wrapper_quirks)
         self.MAX_SLOTS, self.NUM_CATTLE = int(num_drones), int(num_cattle)
         self.PYB_FREQ, self.CTRL_FREQ = int(pyb_freq), int(ctrl_freq)
         self.CTRL_TIMESTEP = 1.0 / self.CTRL_FREQ
@@ -126,6 +131,8 @@ class RLlibMultiAgentWrapper(_MultiAgentEnv):
         super().__init__()
         cfg = dict(env_config or {})
         cfg.setdefault("gui", False)
+        # opt-in: report what the REFERENCE wrapper reports (its second invocation of the stateful per-agent functions)
+        cfg["wrapper_quirks"] = bool(cfg.pop("reference_wrapper_quirks", False))
         self.env = MARLCattleAviary(**cfg)
         self._set_agents(self.env.MAX_SLOTS)
 
@@ -160,6 +167,8 @@ class RLlibMultiAgentWrapper(_MultiAgentEnv):
         self.agents = [aid for aid in self.agents if not dones.get(aid, False)]
         dones["__all__"] = len(self.agents) == 0
         truncs["__all__"] = len(self.agents) == 0
+        if self.env.wrapper_quirks:      # the kernel keeps the same list (ChsStateView.active_agents): they must agree
+            assert dones["__all__"] == d["__all__"], "agent list out of step with the simulator's"
         return obs, rewards, dones, truncs, infos
 
     def render(self, mode="human"):

@@ -172,9 +172,11 @@ class DevicePPO:
         self.policy = MlpActorCritic(self.obs_dim, self.act_dim, base["hidden"], base["log_std_init"]).to(dev)
         import torch.distributed as dist
         multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        # minibatch update as a graph: single GPU only (capturing the NCCL gradient all-reduce inside it hung on 2 x B200
-        # with this torch / NCCL pair, so per-GPU learners run their update eagerly)
-        self.cuda_graphs = ((not multi) if cuda_graphs is None else bool(cuda_graphs)) and not multi
+        # minibatch update as CUDA graphs.  One GPU: one graph per minibatch step.  Per-GPU learners: TWO graphs with the
+        # NCCL gradient all-reduce launched eagerly in between (capturing the collective inside the graph hung on 2 x B200
+        # with this torch / NCCL pair): forward + backward into one flat gradient buffer | all-reduce | clip + Adam
+        self.multi = multi
+        self.cuda_graphs = True if cuda_graphs is None else bool(cuda_graphs)
         # the rollout has no collective in it (envs are sharded, nothing is exchanged): its graph is safe on every rank
         self.graph_rollout = True if cuda_graphs is None else bool(cuda_graphs)
         self.opt = torch.optim.Adam(self.policy.parameters(), lr=base["learning_rate"], eps=1e-5, capturable=self.cuda_graphs)
@@ -189,7 +191,8 @@ class DevicePPO:
         self._acc = torch.zeros((4,), **f)            # sums of pg, vf, ent, clipfrac over the minibatches of an update
         self.num_timesteps = 0
         self._obs = None
-        self._g_roll = self._g_upd = None
+        self._g_roll = self._g_upd = self._g_upd_b = None
+        self._flat = None
         self.last = {}
 
     # ---- views of the simulator's outputs as (B, ...) samples --------------------------------------------------
@@ -276,6 +279,69 @@ class DevicePPO:
         with torch.no_grad():
             self._acc += torch.stack([pg.detach(), vf.detach(), ent.detach(), clipfrac.detach()])
 
+    # ---- per-GPU learners: the same minibatch step cut in two around the gradient all-reduce ------------------------------
+    def _bind_flat_grads(self):
+        """Gradients of all parameters live in ONE flat buffer (p.grad are views of it): the all-reduce needs no packing
+        and both halves of the step see fixed addresses, which is what lets them be captured separately."""
+        n = sum(p.numel() for p in self._params)
+        self._flat = torch.zeros((n,), dtype=torch.float32, device=self.env.device)
+        o = 0
+        for p in self._params:
+            p.grad = self._flat[o:o + p.numel()].view_as(p)
+            o += p.numel()
+
+    def _mb_forward_backward(self, idx):
+        hp, buf = self.hp, self.buf
+        N = self.n_steps * self.B
+        obs, act = buf["obs"].reshape(N, -1), buf["act"].reshape(N, -1)
+        loss, pg, vf, ent, clipfrac = ppo_loss(self.policy, obs[idx], act[idx], buf["logp"].reshape(N)[idx], buf["adv"].reshape(N)[idx],
+                                               buf["ret"].reshape(N)[idx], buf["w"].reshape(N)[idx], hp)
+        self._flat.zero_()                 # backward accumulates into the views
+        loss.backward()
+        with torch.no_grad():
+            self._acc += torch.stack([pg.detach(), vf.detach(), ent.detach(), clipfrac.detach()])
+
+    def _mb_apply(self):
+        import torch.distributed as dist
+        with torch.no_grad():
+            self._flat.mul_(1.0 / dist.get_world_size())
+        if self.hp["max_grad_norm"]:
+            nn.utils.clip_grad_norm_(self._params, self.hp["max_grad_norm"])
+        self.opt.step()
+
+    def _minibatch_step_multi(self, idx):
+        import torch.distributed as dist
+        self._mb_forward_backward(idx)
+        dist.all_reduce(self._flat)
+        self._mb_apply()
+
+    def _capture_update_multi(self):
+        """Two captures sharing the flat gradient buffer; the eager all-reduce between their replays is stream-ordered."""
+        import torch.distributed as dist
+        dev = self.env.device
+        saved_p = [p.detach().clone() for p in self._params]
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self._minibatch_step_multi(self._idx)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self._g_upd, self._g_upd_b = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._g_upd, capture_error_mode="thread_local"):
+            self._mb_forward_backward(self._idx)
+        dist.all_reduce(self._flat)
+        with torch.cuda.graph(self._g_upd_b, capture_error_mode="thread_local"):
+            self._mb_apply()
+        with torch.no_grad():                       # undo the warm-up and the capture passes
+            for p, q in zip(self._params, saved_p):
+                p.copy_(q)
+            for st in self.opt.state.values():
+                for v in st.values():
+                    if torch.is_tensor(v):
+                        v.zero_()
+        torch.cuda.synchronize(dev)
+
     def _capture_update(self):
         """Whole-step capture (PyTorch CUDA-graph recipe): a few eager steps on a side stream, whose effect on the
         weights and the optimizer state is undone, then one captured step that every minibatch replays."""
@@ -307,16 +373,29 @@ class DevicePPO:
         self._params = list(self.policy.parameters())
         dev = self.env.device
         graphs = self.cuda_graphs and N % self.batch_size == 0
+        if self.multi and self._flat is None:
+            self._bind_flat_grads()
         if graphs and self._g_upd is None:
-            self._capture_update()
+            if self.multi:
+                self._capture_update_multi()
+            else:
+                self._capture_update()
         self._acc.zero_()
         n_mb = 0
+        import torch.distributed as dist
         for _ in range(hp["n_epochs"]):
             perm = torch.randperm(N, device=dev)
             for s in range(0, N, self.batch_size):
-                if graphs:
+                if graphs and self.multi:
+                    self._idx.copy_(perm[s:s + self.batch_size])
+                    self._g_upd.replay()              # forward + backward into the flat gradient buffer
+                    dist.all_reduce(self._flat)       # NCCL over NVLink, eager, stream-ordered between the two graphs
+                    self._g_upd_b.replay()            # 1/world, clip, Adam
+                elif graphs:
                     self._idx.copy_(perm[s:s + self.batch_size])
                     self._g_upd.replay()
+                elif self.multi:
+                    self._minibatch_step_multi(perm[s:s + self.batch_size])
                 else:
                     self._minibatch_step(perm[s:s + self.batch_size])
                 n_mb += 1

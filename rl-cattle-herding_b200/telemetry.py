@@ -2,11 +2,27 @@
 
 `utils/evaluation.py:5-94` keeps per-step and per-episode lists on the host and pickles them as one dict
 (`save_evaluation_data`); `utils/pickel_me_this.py` plots from that file.  `EvaluationLog` produces the same dict
-(same keys, same nesting: episode -> step -> per-entity arrays) from the simulator's state, for the few envs an
-evaluation run watches.  The per-step arithmetic follows `BaseAviary.update_evaluation_metrics`
-(sb3_envs/BaseAviary.py:1406-1435) including its quirks: the running "distance" of a drone is a 2-vector that starts
-at the drone's spawn position (:683-688) and grows by 1.7 x the xy step length in both components (:1424), and the
-first step is measured from the origin because `last_drones_pos` is zeroed by reset (:317).
+(same keys, same nesting: episode -> step -> per-entity arrays) for one watched environment.  The numbers that the
+reference accumulates step by step come from the simulator's own device-side accumulators -- the per-drone running path
+length (`ChsStateView.path_len`, kept by the step kernel) and the herded-cow count of the step (`chs_set_debug_buffers`)
+-- the poses the schema stores per step come from one `chs_get_state` of that env.
+
+Pinned to a pickle written by the unmodified reference (`tests/golden/eval/`, `oracle/ref_harness/make_eval_golden.py`),
+including the reference's ordering and aliasing quirks:
+  * `update_evaluation_metrics` (sb3_envs/BaseAviary.py:1406-1435) runs BEFORE the step counter advances (:462-464), so
+    `time_per_step` / `time_taken` use the pre-increment counter;
+  * the running "distance" of a drone is a 2-vector that starts at ZERO (`_housekeeping` reads the position cache before
+    the first kinematics refresh, :683-688 vs :322) and grows by 1.7 x the xy step length in both components (:1424);
+    the first step is measured from the origin because `last_drones_pos` is zeroed by reset (:317);
+  * `evaluation_episode_trigger` (:1439-1450) fires inside `_computeTruncated` on the time limit only
+    (CattleAviary.py:545-550), i.e. before that step's per-step append -- the truncating step's sample opens the NEXT
+    logged episode -- and twice per step, because `_computeReward` calls `_computeTruncated` as well (:315), so every
+    time-limit episode is followed by an empty one;
+  * the per-step buffers are only cleared by that trigger: samples of episodes that end any other way stay in them;
+  * the log stores the list object `episode_drone_distances` itself, which later steps keep updating in place: all entries
+    of one episode alias one list and show its final values (pickle keeps the aliasing);
+  * `cattle_vel_per_step` is the cached velocity from before the step's herd update (`_getCowStateVector` reads the
+    cache filled at :425, `_flockingStep` writes the store afterwards, :1398-1400).
 """
 import pickle
 
@@ -46,55 +62,58 @@ class EvaluationLog:
     def __init__(self, sim, env_index=0):
         self.sim, self.e = sim, int(env_index)
         self.data = {k: [] for k in KEYS}
-        self._new_episode()
+        self._cur = {k: [] for k in KEYS if k.endswith("_per_step")}      # evaluator.curr_*: cleared by the trigger only
+        self._dist, self._cvel, self._n = [], None, 0
+        if sim._dbg_herd is None:
+            sim.enable_debug_outputs()
 
-    def _new_episode(self):
-        self._cur = {k: [] for k in KEYS if k.endswith("_per_step")}
-        self._dist, self._last = None, None
+    def state(self):
+        return self.sim.get_state(self.e, 1)
 
-    def _state(self):
-        s = self.sim.get_state(self.e, 1)
-        n = int(s["n_drones"][0])
-        return s, n
+    def _effectiveness(self):
+        """Herded-cow count of the last step, as the step kernel's winding-number pass left it on the device."""
+        return int(self.sim._dbg_herd[self.e].item()) / self.sim.num_cattle * 100.0     # utils/evaluation.py:136
 
-    def on_reset(self):
-        """After `reset()`: distances start at the spawn positions, `last_drones_pos` at the origin."""
-        s, n = self._state()
-        self._new_episode()
-        self._dist = [s["pos"][0, i, :2].astype(np.float32).copy() for i in range(n)]
-        self._last = [np.zeros(2) for _ in range(n)]
+    def on_reset(self, s=None):
+        """After `reset()` (`_housekeeping` :683-688 and `reset` :317): a NEW distances list, starting at zero."""
+        s = self.state() if s is None else s
+        self._n = int(s["n_drones"][0])
+        self._dist = [np.zeros(2) for _ in range(self._n)]
+        self._cvel = s["cattle_vel"][0, :, :2].copy()
 
-    def on_step(self):
-        """After every `step()` (`update_evaluation_metrics`)."""
-        s, n = self._state()
-        if self._dist is None or len(self._dist) != n:
-            self.on_reset()
-        dpos, dvel = s["pos"][0, :n, :2].copy(), s["vel"][0, :n, :2].copy()
-        cpos, cvel = s["cattle_pos"][0, :, :2].copy(), s["cattle_vel"][0, :, :2].copy()
+    def on_step(self, s=None):
+        """After every `step()`, with the state it left (`update_evaluation_metrics`)."""
+        s = self.state() if s is None else s
+        n = self._n
+        if len(self._dist) != n or self._cvel is None:
+            self.on_reset(s)
+            n = self._n
+        path = np.maximum(s["path_len"][0, :n], 0.0)          # device accumulator; < 0 marks "no step yet"
         for i in range(n):
-            self._dist[i] = self._dist[i] + np.float32(np.linalg.norm(self._last[i] - dpos[i]) * 1.7)
-            self._last[i] = dpos[i].copy()
-        t = int(s["step_counter"][0]) / self.sim.ctrl_freq
+            self._dist[i][:] = path[i]                          # in place: earlier log entries alias this list
+        dpos, dvel = s["pos"][0, :n, :2].copy(), s["vel"][0, :n, :2].copy()
+        cpos = s["cattle_pos"][0, :, :2].copy()
         c = self._cur
-        c["distances_per_step"].append([d.copy() for d in self._dist])
-        c["time_per_step"].append(t)
-        c["effectiveness_per_step"].append(herding_effectiveness(cpos, dpos))
+        c["distances_per_step"].append(self._dist)
+        c["time_per_step"].append((int(s["step_counter"][0]) - self.sim.substeps) / self.sim.ctrl_freq)
+        c["effectiveness_per_step"].append(self._effectiveness())
         c["drone_poses_per_step"].append(dpos)
         c["cattle_poses_per_step"].append(cpos)
         c["drone_vel_per_step"].append(dvel)
-        c["cattle_vel_per_step"].append(cvel)
+        c["cattle_vel_per_step"].append(self._cvel)
+        self._cvel = s["cattle_vel"][0, :, :2].copy()
 
-    def on_episode_end(self):
-        """`evaluation_episode_trigger` (:1439-1450): the reference fires it when the time limit truncates an episode."""
-        s, n = self._state()
+    def on_episode_end(self, s=None):
+        """`evaluation_episode_trigger` (:1439-1450); call it BEFORE `on_step` of the truncating step, twice."""
+        s = self.state() if s is None else s
         d = self.data
-        d["distances"].append([x.copy() for x in (self._dist or [])])
-        d["num_drones"].append(n)
-        d["time_taken"].append(int(s["step_counter"][0]) / self.sim.ctrl_freq)
-        d["effectiveness"].append(herding_effectiveness(s["cattle_pos"][0, :, :2], s["pos"][0, :n, :2]))
+        d["distances"].append(self._dist)
+        d["num_drones"].append(self._n)
+        d["time_taken"].append((int(s["step_counter"][0]) - self.sim.substeps) / self.sim.ctrl_freq)
+        d["effectiveness"].append(self._effectiveness())
         for k, v in self._cur.items():
             d[k].append(v)
-        self._new_episode()
+        self._cur = {k: [] for k in self._cur}
 
     def save(self, save_path="evaluation_data.pkl"):
         """`evaluator.save_evaluation_data` (utils/evaluation.py:73-94): same dict, same default file name."""

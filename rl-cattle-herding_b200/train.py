@@ -41,6 +41,8 @@ def main(argv=None):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from .dist import require_even_shards
+    require_even_shards(args.envs, world)
     first, count = shard_range(args.envs, world, rank)
     marl = args.mode == "dtde"
     level = args.level if args.level is not None else (0 if marl else 7)       # MARLCattleAviary.py:62 / CattleAviary.py:62

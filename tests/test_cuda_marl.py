@@ -142,3 +142,76 @@ def test_marl_auto_reset_and_host_path():
         n_done += int(done.sum())
     assert n_done > 20
     a.close(); b.close()
+
+
+# ---- the reference's RLlib wrapper, bug for bug (ChsParams.marl_wrapper_quirks) ---------------------------------------
+WRAPPER_GOLDEN = ["w_3d20c_uniform", "w_l0_hold_levelup", "w_l2_approach", "w_l4_surround"]
+
+
+class _WGolden(Golden):
+    def __init__(self, name):
+        import json, os
+        from _golden import GOLDEN_DIR
+        z = np.load(os.path.join(GOLDEN_DIR, "wrapper", name + ".npz"))
+        self.name, self.z = name, {k: z[k] for k in z.files}
+        self.meta = json.loads(str(self.z["meta_json"]))
+        self.steps, self.table = self.z["action"].shape[0], self.z["spawn_table"]
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("name", WRAPPER_GOLDEN)
+def test_rllib_wrapper_quirks_teacher_forced(name, precision):
+    """What RLlib sees through the REFERENCE wrapper (rllib_envs/marl_wrapper.py:77-119): rollouts recorded through that
+    wrapper (oracle/ref_harness/make_wrapper_golden.py), step t injected into env t together with the wrapper's agent
+    list, one launch with `marl_wrapper_quirks`: rewards / flags of the second invocation, the state it leaves (spacing
+    clock, tally, level, prev_cent_dist) and the agent list after the step."""
+    g = _WGolden(name)
+    env = _env_for(g, precision, marl_wrapper_quirks=True)
+    ints = INT_STATE + ("active_agents",)
+    env.set_state({k: g.z[f"before_{k}"] for k in FLOAT_STATE + ints})
+    obs, rew, term, trunc = env.step(torch.from_numpy(np.ascontiguousarray(g.z["action"])).cuda())
+    torch.cuda.synchronize()
+    got = env.get_state()
+    obs, rew, term, trunc = obs.cpu().numpy(), rew.cpu().numpy(), term.cpu().numpy(), trunc.cpu().numpy()
+    for k in ints:
+        assert np.array_equal(got[k].astype(np.int64), g.z[f"after_{k}"].astype(np.int64)), (name, k, got[k], g.z[f"after_{k}"])
+    assert np.array_equal(term[:, :D], g.z["terminated"]), (name, "terminated")
+    assert np.array_equal(trunc[:, :D], g.z["truncated"]), (name, "truncated")
+    assert np.array_equal(term[:, D].astype(bool), g.z["term_all"].astype(bool)) and np.array_equal(trunc[:, D].astype(bool), g.z["trunc_all"].astype(bool))
+    for k in FLOAT_STATE:
+        ref = g.z[f"after_{k}"]
+        scale = max(1.0, float(np.max(np.abs(np.where(np.isfinite(ref), ref, 0.0)))))
+        tol = 1e-9 * scale if precision == "fp64" else FP32_REL * scale + FP32_FLOOR.get(k, 1e-6)
+        assert max_err(got[k], ref) <= tol, (name, precision, k, max_err(got[k], ref), tol)
+    # observations: the wrapper returns rows of the agents in its list only (zeros elsewhere in the recording)
+    listed = ((g.z["before_active_agents"][:, None] >> np.arange(D)[None, :]) & 1).astype(bool)
+    ref_obs = g.z["obs"]
+    scale = max(1.0, float(np.max(np.abs(ref_obs))))
+    if precision == "fp32":
+        obs = _mask_near_ties(g, obs, np.where(listed[:, :, None], ref_obs, obs))
+    assert max_err(np.where(listed[:, :, None], obs, 0.0), ref_obs) <= (2e-7 * scale if precision == "fp64" else FP32_REL * scale + 1e-6)
+    _check_rewards(rew, g.z["reward"], 1.2e-7 if precision == "fp64" else 5e-5, (name, precision))
+    env.close()
+
+
+def test_rllib_wrapper_quirks_free_running():
+    """`RLlibMultiAgentWrapper` with `reference_wrapper_quirks`: replays the recorded run from its first state through the
+    dict API (agent list kept by the wrapper AND by the kernel) and lands on the reference wrapper's outputs."""
+    import rl_cattle_herding_b200 as pkg
+    g = _WGolden("w_l0_hold_levelup")
+    m = g.meta
+    w = pkg.RLlibMultiAgentWrapper(dict(num_drones=D, num_cattle=m["n_cattle"], ctrl_freq=m["ctrl_freq"], fixed_num_drones=m["n_drones"],
+                                        curriculum_level=m["start_level"], precision="fp64", spawn_table=g.table,
+                                        reference_wrapper_quirks=True))
+    w.reset()
+    w.env.sim.set_state({k: g.z[f"before_{k}"][:1] for k in FLOAT_STATE + INT_STATE})
+    for t in range(g.steps):
+        assert sum(1 << int(a.split("_")[1]) for a in w.agents) == int(g.z["before_active_agents"][t]), t
+        obs, rew, term, trunc, _ = w.step({aid: g.z["action"][t][int(aid.split("_")[1])] for aid in w.agents})
+        for aid in rew:
+            i = int(aid.split("_")[1])
+            assert abs(rew[aid] - g.z["reward"][t, i]) <= 2e-6 * (1 + abs(g.z["reward"][t, i])), (t, aid)
+            assert term[aid] == bool(g.z["terminated"][t, i]) and trunc[aid] == bool(g.z["truncated"][t, i]), (t, aid)
+        assert term["__all__"] == bool(g.z["term_all"][t]) and trunc["__all__"] == bool(g.z["trunc_all"][t])
+        assert not g.z["reset_after"][t]
+    w.close()

@@ -107,6 +107,25 @@ def test_teacher_forced(name, precision, mode, variant):
     # 2^-24 rounding of ~4 m drone coordinates held in fp32 shows up as ~3e-5 in the reward
     tol = 1.2e-7 if precision == "fp64" else 5e-5
     assert max_err(rew[fin], ref_rew[fin]) <= tol * max(1.0, float(np.max(np.abs(ref_rew[fin])))), (name, precision, "reward")
+    # device-side telemetry accumulators (chs_stats slots 11-15) against the same recordings: path length and effectiveness
+    # of the episodes that ended in this launch (update_evaluation_metrics, BaseAviary.py:1406-1435), per-step
+    # effectiveness, curriculum successes and level-ups (curriculum_learning.py:200-222)
+    st = env.stats()
+    done = (g.z["terminated"] != 0) | (g.z["truncated"] != 0)
+    herd, M = herd.cpu().numpy().astype(np.float64), float(g.meta["n_cattle"])
+    n_dr = g.z["before_n_drones"].astype(int)
+    step_len = np.linalg.norm(g.z["after_pos"][:, :, :2] - g.z["before_pos"][:, :, :2], axis=2)       # (steps, 12)
+    path = np.array([1.7 * step_len[t, : n_dr[t]].sum() for t in range(g.steps)])
+    ptol = 1e-9 if precision == "fp64" else 1e-4
+    assert st[0] == done.sum() and st[10] == g.steps
+    assert st[11] == pytest.approx(path[done].sum(), abs=ptol * max(1, done.sum())), (name, "path length")
+    assert st[12] == pytest.approx((herd[done] / M * 100.0).sum(), abs=1e-9) and st[13] == pytest.approx((herd / M * 100.0).sum(), abs=1e-9)
+    got_path = got["path_len"]
+    assert np.allclose([got_path[t, : n_dr[t]].sum() for t in range(g.steps)], path, rtol=0, atol=ptol), (name, "per-drone path")
+    if name.startswith("l"):      # sb3 packing, levels 0-6: one success per step at most, visible in (level, tally)
+        lvup = g.z["after_level"] != g.z["before_level"]
+        succ = lvup | (g.z["after_tally"] != g.z["before_tally"])
+        assert st[14] == succ.sum() and st[15] == lvup.sum(), (name, st[14], succ.sum(), st[15], lvup.sum())
 
 
 @pytest.mark.parametrize("name", ["a_3d20c_uniform", "d_inherd_4d16c", "e_12d16c_tworow", "l4_surround"])

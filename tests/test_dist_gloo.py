@@ -34,9 +34,13 @@ WORKER = textwrap.dedent("""
     red = chd.reduce_stats(stats)
     import torch
     obs = torch.full((count, 2), float(rank))
-    allobs = chd.gather_observations(obs) if count == 500 else obs
+    allobs = chd.gather_observations(obs)
+    # uneven shards (total %% world != 0): sizes are exchanged first, short shards padded for the collective
+    f2, c2 = chd.shard_range(1001, ws, rank)
+    uneven = chd.gather_observations(torch.full((c2, 3), float(rank)))
     if rank == 0:
-        print(json.dumps({"red": red.tolist(), "ws": ws, "gathered": list(allobs.shape), "sum": chd.summarize(red)["episodes"]}))
+        print(json.dumps({"red": red.tolist(), "ws": ws, "gathered": list(allobs.shape), "sum": chd.summarize(red)["episodes"],
+                          "uneven": list(uneven.shape), "uneven_split": int((uneven[:, 0] == 0).sum())}))
     dist.barrier()
     dist.destroy_process_group()
 """)
@@ -55,6 +59,15 @@ def test_stats_reduction_world_size_2(tmp_path):
     d = json.loads(line)
     assert d["ws"] == 2 and d["red"][0] == 1000 and d["red"][1] == 500.0 and d["red"][10] == 7000.0
     assert d["gathered"] == [1000, 2] and d["sum"] == 1000
+    assert d["uneven"] == [1001, 3] and d["uneven_split"] == 501
+
+
+def test_learners_refuse_uneven_shards():
+    import pytest
+    from rl_cattle_herding_b200 import dist as chd
+    chd.require_even_shards(4096, 8)
+    with pytest.raises(ValueError):
+        chd.require_even_shards(1001, 2)
 
 
 def test_bench_reference_arm_other_ranks_are_silent():

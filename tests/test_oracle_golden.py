@@ -90,3 +90,35 @@ def test_marl_teacher_forced(name):
         assert max_err(rew, g.z["reward"][t]) <= TOL * max(1.0, float(np.max(np.abs(g.z["reward"][t])))), (name, t, "reward")
         n_term += int(term.any()); n_trunc += int(trunc.any())
     assert n_term + n_trunc >= 1
+
+
+@pytest.mark.parametrize("name", ["w_3d20c_uniform", "w_l0_hold_levelup", "w_l2_approach", "w_l4_surround"])
+def test_rllib_wrapper_teacher_forced(name):
+    """The reference's RLlib wrapper (rllib_envs/marl_wrapper.py:77-119), recorded through the wrapper itself
+    (tests/golden/wrapper, oracle/ref_harness/make_wrapper_golden.py): second invocation of the stateful per-agent
+    functions for the agents in its list, list update, "__all__" = list empty."""
+    import json, os
+    from _golden import GOLDEN_DIR
+    z = np.load(os.path.join(GOLDEN_DIR, "wrapper", name + ".npz"))
+    meta = json.loads(str(z["meta_json"]))
+    import cattle_oracle as co
+    env = co.OracleEnv(meta["n_cattle"], ctrl_freq=meta["ctrl_freq"], pyb_freq=meta["pyb_freq"], start_level=meta["start_level"],
+                       spawn_table=z["spawn_table"], act=meta["act"])
+    masks = set()
+    for t in range(z["action"].shape[0]):
+        env.set_state({k: z[f"before_{k}"][t] for k in co.STATE_FIELDS})
+        obs, rew, term, trunc, mask = env.step_rllib_wrapper(z["action"][t], int(z["before_active_agents"][t]))
+        got = env.get_state()
+        for k in INT_STATE:
+            assert int(got[k]) == int(z[f"after_{k}"][t]), (name, t, k)
+        assert mask == int(z["after_active_agents"][t]), (name, t)
+        assert np.array_equal(term, z["terminated"][t].astype(bool)) and np.array_equal(trunc, z["truncated"][t].astype(bool)), (name, t)
+        assert bool(z["term_all"][t]) == (mask == 0) and bool(z["trunc_all"][t]) == (mask == 0)
+        for k in FLOAT_STATE:
+            ref = z[f"after_{k}"][t]
+            scale = max(1.0, float(np.nanmax(np.abs(np.where(np.isfinite(ref), ref, 0.0)))))
+            assert max_err(got[k], ref) <= TOL * scale, (name, t, k)
+        assert max_err(obs, z["obs"][t]) <= 2e-7 * max(1.0, float(np.max(np.abs(z["obs"][t])))), (name, t, "obs")
+        assert max_err(rew, z["reward"][t]) <= TOL * max(1.0, float(np.max(np.abs(z["reward"][t])))), (name, t, "reward")
+        masks.add(int(z["before_active_agents"][t]))
+    assert len(masks) >= 1

@@ -1,5 +1,5 @@
 """Per-phase latency of the fused step kernel from in-kernel clock64() stamps (GPU box).
-    python tools/phase_timing.py [envs] [G] [threads]"""
+    python tools/phase_timing.py [envs] [G] [threads] [drones] [cattle]"""
 import ctypes as C
 import os
 import sys
@@ -14,7 +14,8 @@ import rl_cattle_herding_b200 as pkg  # noqa: E402
 E = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 G = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 TH = int(sys.argv[3]) if len(sys.argv) > 3 else 128
-N, M = 3, 20
+N = int(sys.argv[4]) if len(sys.argv) > 4 else 3
+M = int(sys.argv[5]) if len(sys.argv) > 5 else 20
 env = pkg.CattleHerdingBatchedEnv(E, num_drones=N, num_cattle=M, fixed_num_drones=N, spawn_table=pkg.spawn.generate(100, M),
                                   device=0, envs_per_block=G, threads_per_block=TH)
 env.reset()
@@ -50,6 +51,7 @@ def span(a, b):
     return (c[:, b] - c[:, a]).mean()
 print("  p1 detail: start->action/PID done %.0f, substeps+euler %.0f, stores %.0f" % (span(2, 16), span(16, 17), span(17, 3)))
 print("  p2 detail: neighbours %.0f, cattle obs loop %.0f, herd finish %.0f, winding %.0f" % (span(4, 19), span(19, 20), span(20, 21), span(21, 5)))
+print("  p2 neighbours detail: ranking loop %.0f, obs slots %.0f, spacing rewards %.0f, tail %.0f" % (span(4, 24), span(24, 25), span(25, 26), span(26, 19)))
 print("  p3 detail: reward->stats done %.0f, env stores %.0f, bulk issue %.0f" % (span(8, 22), span(22, 23), span(23, 9)))
 tot = c[:, 12] - c[:, 0]
 p5 = c[:, 12] - c[:, 11]
