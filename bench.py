@@ -489,6 +489,10 @@ def run_cuda_arm(args):
                              f"({rot.R * rot.touched_per_env * E / 1e6:.0f} MB touched per round > 126 MB L2), no flush kernel",
                        "timing": "one CUDA-event pair on the launching stream around a CUDA graph of exactly K consecutive steps "
                                  "(one kernel node per step), barrier + synchronize on both sides, max over ranks",
+                       "launch_mode": ("plain launches (CHS_NO_PDL)" if os.environ.get("CHS_NO_PDL") else
+                                       "programmatic dependent launch: a step kernel's launch and shared-memory prologue overlap the "
+                                       "tail of the previous kernel of the stream; it executes griddepcontrol.wait (the previous "
+                                       "kernel complete, its memory visible) before its first global-memory access"),
                        "sharding": "env index, no collective on the step path; one NCCL all-reduce of the stats vector after the run",
                        "rank_cores": cores},
             "drone_steps_per_s": value * N,

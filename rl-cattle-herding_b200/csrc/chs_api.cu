@@ -65,6 +65,7 @@ struct ChsHandle {
   unsigned char* h_small;           // pinned mirror
   struct { const void* ptr; size_t bytes; } zeroed_host[4];   // pageable host buffers whose padding rows were zero-filled (chs_api_io.inc)
   unsigned zeroed_next;
+  bool knob_no_pdl;                 // CHS_NO_PDL=1: plain launches, no programmatic dependent launch
   bool knob_no_direct;              // CHS_NO_DIRECT=1: the host path stages through HBM even for pinned buffers
   int knob_smem_pad;
   bool knob_full, knob_inline_reset;
@@ -250,6 +251,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   kp.early_ok = getenv("CHS_NO_EARLY") ? 0 : 1;
   h->knob_inline_reset = getenv("CHS_INLINE_RESET") != nullptr;
   h->knob_no_direct = getenv("CHS_NO_DIRECT") != nullptr;
+  h->knob_no_pdl = getenv("CHS_NO_PDL") != nullptr;
   kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
   kp.wrapper_quirks = (prm->marl_wrapper_quirks && prm->packing == CHS_PACK_MARL) ? 1 : 0;
@@ -456,13 +458,28 @@ extern "C" int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_d
   return rc;
 }
 
+// Launch of one kernel of the step path with programmatic dependent launch allowed (chs_kernel.cuh: pdl_wait): the launch
+// latency and the kernel's prologue overlap the tail of whatever kernel precedes it on the stream; every kernel launched
+// through here executes griddepcontrol.wait before its first global-memory access.  CHS_NO_PDL=1 launches plainly (A/B runs).
+template <typename K, typename A>
+static void launch_pdl(const ChsHandle* h, K kernel, unsigned grid, unsigned threads, size_t smem, cudaStream_t st, const A& a) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = h->knob_no_pdl ? 0 : 1;
+  cudaLaunchKernelEx(&cfg, kernel, a);
+}
+
 template <typename T> static void launch_step_variant(ChsHandle* h, const KArgs<T>& a, int grid, cudaStream_t st);
 #define CHS_LAUNCH(TT, MT, MB, FL)                                                                                 \
   do {                                                                                                               \
-    if (marl) { if (split) step_kernel<TT, MT, MB, true, true, FL><<<grid, h->threads, h->smem, st>>>(a);            \
-                else step_kernel<TT, MT, MB, true, false, FL><<<grid, h->threads, h->smem, st>>>(a); }               \
-    else      { if (split) step_kernel<TT, MT, MB, false, true, FL><<<grid, h->threads, h->smem, st>>>(a);           \
-                else step_kernel<TT, MT, MB, false, false, FL><<<grid, h->threads, h->smem, st>>>(a); }              \
+    if (marl) { if (split) launch_pdl(h, step_kernel<TT, MT, MB, true, true, FL>, grid, h->threads, h->smem, st, a);  \
+                else launch_pdl(h, step_kernel<TT, MT, MB, true, false, FL>, grid, h->threads, h->smem, st, a); }     \
+    else      { if (split) launch_pdl(h, step_kernel<TT, MT, MB, false, true, FL>, grid, h->threads, h->smem, st, a); \
+                else launch_pdl(h, step_kernel<TT, MT, MB, false, false, FL>, grid, h->threads, h->smem, st, a); }    \
   } while (0)
 template <> void launch_step_variant<double>(ChsHandle* h, const KArgs<double>& a, int grid, cudaStream_t st) {
   const bool marl = h->kp.packing == CHS_PACK_MARL, split = a.p.split != 0;
@@ -496,7 +513,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
     if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
     const long long nthr = (long long)h->kp.D * h->E;
     if (h->kp.auto_reset && !h->knob_inline_reset) a.done_count = h->done_count;
-    drone_kernel<T><<<(unsigned)((nthr + 255) / 256), 256, 0, st>>>(a);
+    launch_pdl(h, drone_kernel<T>, (unsigned)((nthr + 255) / 256), 256, 0, st, a);
     a.p.split = 1;
   }
   const bool defer = split && h->kp.auto_reset && !h->knob_inline_reset;
@@ -505,7 +522,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   if (defer) {
     KArgs<T> r = base_args<T>(h);
     r.done_list = h->done_list; r.done_count = h->done_count; r.obs = obs;
-    reset_list_kernel<T><<<148 * 8, 256, 0, st>>>(r);
+    launch_pdl(h, reset_list_kernel<T>, 148 * 8, 256, 0, st, r);
   }
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;
@@ -557,7 +574,7 @@ static int launch_step_static(ChsHandle* h, unsigned char* scratch, const float*
   const bool defer = h->kp.auto_reset != 0;
   if (defer) a.done_count = count;
   const long long nthr = (long long)D * (long long)E;
-  drone_kernel<T><<<(unsigned)((nthr + 255) / 256), 256, 0, st>>>(a);
+  launch_pdl(h, drone_kernel<T>, (unsigned)((nthr + 255) / 256), 256, 0, st, a);
   a.p.split = 1;
   if (defer) { a.done_list = list; a.done_count = count; }
   const int grid = (h->E + h->kp.G - 1) / h->kp.G;
@@ -565,7 +582,7 @@ static int launch_step_static(ChsHandle* h, unsigned char* scratch, const float*
   if (defer) {
     KArgs<T> r = base_args<T>(h);
     r.done_list = list; r.done_count = count; r.obs = obs;
-    reset_list_kernel<T><<<148 * 8, 256, 0, st>>>(r);
+    launch_pdl(h, reset_list_kernel<T>, 148 * 8, 256, 0, st, r);
   }
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;

@@ -112,6 +112,14 @@ __device__ __forceinline__ void bulk_store_live(const KParams& p, const float* s
   if (c1 > cur) bulk_store(out + cur, src + cur, c1 - cur);
 }
 
+// Programmatic dependent launch (PDL): every kernel of the step path is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so its CTAs may become resident -- and run whatever precedes pdl_wait()
+// -- while the previous kernel of the stream is still draining.  pdl_wait() returns once that kernel has completed and its
+// memory is visible; NOTHING that touches global memory may precede it.  pdl_launch_next() lets the next kernel of the stream
+// (if it opted in the same way) start its own prologue.  Both are no-ops for a launch without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_next() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -353,7 +361,9 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
   const int cbase = (p.packing == CHS_PACK_MARL) ? 10 + 2 * 4 : 10 + 2 * CHS_MAX_DRONES;
   const int nobs = (M < 16) ? M : 16;
   const typename VT<T>::v2* srow = a.spawn + (size_t)row * p.spawn_stride;
-  if (parts & RESET_COWS) for (int j = lane; j < M; j += 32) {                       // cows (BaseAviary.py:611-637)
+#define CHS_COLD_LOOP _Pragma("unroll 1")
+  // this code runs once per finished env, cold: every instruction is an instruction-cache miss, so its loops stay rolled
+  if (parts & RESET_COWS) CHS_COLD_LOOP for (int j = lane; j < M; j += 32) {                       // cows (BaseAviary.py:611-637)
     const auto xy = srow[j];
     uint32_t c[4] = {(uint32_t)(p.env_id_offset + e), (uint32_t)epi, (uint32_t)j, (uint32_t)TAG_COW};
     philox4x32_10(c, p.seed_lo, p.seed_hi);
@@ -389,7 +399,7 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
     T mx, my;
     spawn_xy<T>(lane, n, mx, my);
     T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
-    for (int j = 0; j < n; ++j) {
+    CHS_COLD_LOOP for (int j = 0; j < n; ++j) {
       if (j == lane) continue;
       T ox, oy;
       spawn_xy<T>(j, n, ox, oy);
@@ -404,13 +414,13 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
   T cow_c = T(0);
   const bool cow_ok = (lane >> 1) < nobs;
   if (cow_ok) { const auto xy = srow[lane >> 1]; cow_c = (lane & 1) ? xy.y : xy.x; }
-  for (int d = 0; d < n && d < p.R; ++d) {
+  CHS_COLD_LOOP for (int d = 0; d < n && d < p.R; ++d) {
     T mx, my;
     spawn_xy<T>(d, n, mx, my);
     const int nb1 = __shfl_sync(full, j1, d), nb2 = __shfl_sync(full, j2, d);
     float* orow = ob + d * L;
     {   // columns 0 .. cbase-1: z, zeros, two neighbour slots, zeros (cbase <= 34: two passes at most)
-      for (int c = lane; c < cbase; c += 32) {
+      CHS_COLD_LOOP for (int c = lane; c < cbase; c += 32) {
         float v = 0.f;
         if (c == 0) v = (float)T(k::TARGET_ALT);
         else if (c >= 10 && c < 14) {
@@ -421,12 +431,12 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
       }
     }
     if (cbase + lane < L) orow[cbase + lane] = cow_ok ? (float)(cow_c - ((lane & 1) ? my : mx)) : 0.f;
-    for (int c = cbase + 32 + lane; c < L; c += 32) orow[c] = 0.f;
+    CHS_COLD_LOOP for (int c = cbase + 32 + lane; c < L; c += 32) orow[c] = 0.f;
   }
   const int zfrom = (n < p.R ? n : p.R) * L;
   if (p.pad_persist) {   // rows >= D are the caller's constant zeros; only unused drone slots (n < D) are cleared
     const int zend = (D < p.R ? D : p.R) * L;
-    for (int idx = zfrom + lane; idx < zend; idx += 32) ob[idx] = 0.f;
+    CHS_COLD_LOOP for (int idx = zfrom + lane; idx < zend; idx += 32) ob[idx] = 0.f;
   } else if (p.vec4_ok) {       // R*L is a multiple of 4 and the image is 16-byte aligned: the zero rows go out as float4
     const int z4 = (zfrom + 3) >> 2;
     if (zfrom + lane < (z4 << 2)) ob[zfrom + lane] = 0.f;        // up to 3 floats to the next 16-byte boundary
@@ -473,6 +483,8 @@ __global__ void __launch_bounds__(256) reset_list_kernel(const KArgs<T> a) {
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  pdl_wait();
+  pdl_launch_next();
   const int count = *a.done_count;
   for (int i = gw; i < count; i += nwarps) {
     const int e = a.done_list[i];
@@ -503,6 +515,8 @@ __global__ void __launch_bounds__(256) drone_kernel(const KArgs<T> a) {
   const KParams& p = a.p;
   const int E = p.E, D = p.D;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  pdl_wait();
+  pdl_launch_next();
   if (idx == 0 && a.done_count) *a.done_count = 0;      // the list of finished envs is rebuilt by this step's step_kernel
   if (idx >= (long long)D * E) return;
   const int d = (int)(idx / E), e = (int)(idx - (long long)d * E);
@@ -570,6 +584,22 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   // ---------------- phase 0 ----------------
   // Every global read the step needs is issued here, before the first barrier, so that the DRAM round trips
   // of the herd, the env scalars and the first drone item of each drone thread overlap.
+  // Early start of the drone chain: with a single drone warp (warp 0) and other warps to do the staging, warp 0 only
+  // ARRIVES at the barrier that closes phase 0 and goes straight into its serial chain as soon as its own loads land;
+  // it neither stages the herd nor waits for the copies of the others.  It meets the staging warps again on named
+  // barrier 1 just before its first shared-memory write (the staging area has to be zeroed by then).
+  const bool early = !SPLIT && p.early_ok && ndt == 32 && nt > 32 && (!FULL || (p.cp_ok && !(p.aero_flags & 4)));
+  const int sw0 = early ? ndt : 0;           // first thread that takes part in the staging loops
+  const int snt = nt - sw0, sw = t - sw0;    // sw < 0: exempt
+  // prologue (no global memory): the observation staging area and the zero block are cleared while, under PDL, the
+  // previous kernel of the stream is still draining
+  if (sw >= 0) {
+    const int nq = (G * p.stage_stride) >> 2;
+    float4* st4 = reinterpret_cast<float4*>(s.stage);
+    for (int i = sw; i < nq; i += snt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = sw; i < (p.zero_bytes >> 4); i += snt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  pdl_wait();
   int4 pre_i = make_int4(0, 0, 0, 0), pre_j = make_int4(0, 0, 0, 0);
   double2 pre_f = make_double2(0.0, 0.0);
   double pre_ret = 0.0;
@@ -603,13 +633,6 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       for (int i = 0; i < 4; ++i) if (i < p.A) act0[i] = ap[i];
     }
   }
-  // Early start of the drone chain: with a single drone warp (warp 0) and other warps to do the staging, warp 0 only
-  // ARRIVES at the barrier that closes phase 0 and goes straight into its serial chain as soon as its own loads land;
-  // it neither stages the herd nor waits for the copies of the others.  It meets the staging warps again on named
-  // barrier 1 just before its first shared-memory write (the staging area has to be zeroed by then).
-  const bool early = !SPLIT && p.early_ok && ndt == 32 && nt > 32 && (!FULL || (p.cp_ok && !(p.aero_flags & 4)));
-  const int sw0 = early ? ndt : 0;           // first thread that takes part in the staging loops
-  const int snt = nt - sw0, sw = t - sw0;    // sw < 0: exempt
   {
     using V2 = typename VT<T>::v2;
     if (!FULL || p.cp_ok) {
@@ -639,12 +662,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     // curriculum table: 76 chunks of 16 bytes
     if (sw >= 0) for (int it = sw; it < 76; it += snt) cp_async16(s.ctab + 2 * it, a.tab + 2 * it, 16);
     cp_async_commit();
-    const int nq = (G * p.stage_stride) >> 2;
-    float4* st4 = reinterpret_cast<float4*>(s.stage);
-    if (sw >= 0) {
-      for (int i = sw; i < nq; i += snt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int i = sw; i < (p.zero_bytes >> 4); i += snt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    pdl_launch_next();        // every load of this step is in flight: the next kernel of the stream may start its prologue
     if (FULL && !p.cp_ok) {
       for (int it = t; it < M * G; it += nt) {
         const int g = it & (G - 1), j = it >> lg, e = e0 + g;
@@ -855,35 +873,6 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     }
   }
   CHS_STAMP(19);
-#if CHS_EXP & 1
-  // Warp roles of phase 2: the drone warps rank their neighbours and nothing else (they are the critical path of the CTA: they
-  // come out of the serial drone chain last); of the other warps the first `cw` take the cattle pieces of the observation
-  // (lane-cooperative, shuffles inside a warp), the rest the per-cow herd update and the winding numbers.  A CTA without
-  // two spare warps keeps everything on all threads.
-  const int spare_w = (nt - ndt) >> 5;
-  const bool roles = (ndt < nt) && spare_w >= 2;
-  const int cw = roles ? (spare_w >= 4 ? spare_w >> 2 : 1) : 0;
-  {
-    const int c0 = roles ? ndt : 0, cn = roles ? (cw << 5) : nt;         // coop threads [c0, c0 + cn)
-    const int tb = roles ? t - c0 : ((t >= ((nt >> 1) & ~31)) ? t - ((nt >> 1) & ~31) : t + nt - ((nt >> 1) & ~31));
-    if (tb >= 0 && tb < cn) {
-      int lc;
-      if (roles) { lc = 0; while (lc < 3 && ((DG << lc) % cn) != 0) ++lc; }     // fewest lanes per item that fill every round
-      else { lc = 3; while (lc > 0 && (DG << lc) > cn) --lc; }
-      const int C = 1 << lc, items = DG << lc;
-      for (int base = 0; base < items; base += cn) {
-        const int idx = base + tb, it = idx >> lc, sub = idx & (C - 1);
-        const int g = it & (G - 1), d = it >> lg;
-        const bool valid = idx < items && e0 + g < E && d < s.n[g];
-        drone_cattle_coop<T>(p, valid, g, d, sub, C, true, s.dpos, s.cpos, s.redB, s.stage);
-      }
-    }
-  }
-  CHS_STAMP(20);
-  const int pw0 = roles ? ndt + (cw << 5) : ((ndt < nt) ? ndt : 0);
-  const int pnw = nt - pw0;
-  const int pw = t - pw0;               // < 0 on the warps with another role
-#else
   {
     // cattle pieces: C lanes per (drone, env) item, as many as the CTA has threads for (up to 8), on threads half a CTA away
     // from the drone warps; every thread runs the same number of rounds (the lanes of an item meet in shuffles)
@@ -905,7 +894,6 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   const int pw0 = (ndt < nt) ? ndt : 0;
   const int pnw = nt - pw0;
   const int pw = t - pw0;               // < 0 on the drone warps when they are exempt
-#endif
   if (!FULL || !p.cattle_integrate) {
     if (pw >= 0) for (int it = pw; it < nact * M; it += pnw) {
       const int g = s.flist[it % nact], i = it / nact, e = e0 + g;

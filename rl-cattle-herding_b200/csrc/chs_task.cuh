@@ -1,6 +1,9 @@
 // Task layer: reward shapes, success / truncation tests and observation pieces of
 // sb3_envs/CattleAviary.py:213-332,422-552,572-679 and sb3_envs/BaseRLAviary.py:272-342.
 #pragma once
+#ifndef CHS_EXP
+#define CHS_EXP 0
+#endif
 #include "chs_layout.cuh"
 
 namespace chs {
@@ -68,13 +71,18 @@ __device__ __forceinline__ void drone_neighbors(const KParams& p, const double* 
   // a NaN distance never wins '<', and numpy's stable argsort puts NaN last as well
   T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
   int j1 = -1, j2 = -1;
+  // branch free: the drone itself enters with an infinite distance, which never wins a strict '<' (lanes of a warp hold
+  // different drones, so a `continue` on j == d splits the warp in every iteration)
+#pragma unroll 1
   for (int j = 0; j < n; ++j) {
-    if (j == d) continue;
     const auto o = s_dpos[j * G + g];
     const T dx = o.x - me.x, dy = o.y - me.y;
-    const T dist = Mth<T>::sqrt(dx * dx + dy * dy);
-    if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
-    else if (dist < d2) { d2 = dist; j2 = j; }
+    const T dist = (j == d) ? Mth<T>::inf() : Mth<T>::sqrt(dx * dx + dy * dy);
+    const bool lt1 = dist < d1, lt2 = dist < d2;
+    d2 = lt1 ? d1 : (lt2 ? dist : d2);
+    j2 = lt1 ? j1 : (lt2 ? j : j2);
+    d1 = lt1 ? dist : d1;
+    j1 = lt1 ? j : j1;
   }
   if (clk) clk[0] = clock64();
   float* row = s_stage + (size_t)g * p.stage_stride + d * p.L;
