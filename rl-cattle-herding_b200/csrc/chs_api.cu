@@ -229,8 +229,11 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   }
   kp.ctrl_freq = prm->ctrl_freq;
   kp.env_id_offset = prm->env_id_offset;
-  kp.stage_stride = (kp.D * kp.L + 3) & ~3;
-  if ((kp.stage_stride & 31) == 0) kp.stage_stride += 4;
+  kp.stage_copy = (kp.D * kp.L + 3) & ~3;
+  // env stride of the staging area: a multiple of 4 floats (16-byte bulk-store sources) that is 4 mod 8, so that the
+  // consecutive envs held by the lanes of a warp fall into 8 different banks (a stride of 0 mod 8 folds them onto 4 or fewer)
+  kp.stage_stride = kp.stage_copy;
+  while ((kp.stage_stride & 7) != 4) kp.stage_stride += 4;
   kp.vec4_ok = ((kp.R * kp.L) % 4 == 0) ? 1 : 0;
   kp.bulk_ok = (kp.vec4_ok && !getenv("CHS_NO_BULK")) ? 1 : 0;
   // persistent padding needs real padding rows and float4-addressable images (the reset kernel zero-fills them)
@@ -242,7 +245,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
     kp.dead_hi = 10 + 2 * CHS_MAX_DRONES;    // padded to GLOBAL_MAX_NUM_DRONES slots (BaseRLAviary.py:313-314)
   }
   {
-    const int total = kp.R * kp.L * 4, c1 = kp.stage_stride * 4 < total ? kp.stage_stride * 4 : total;
+    const int total = kp.R * kp.L * 4, c1 = kp.stage_copy * 4 < total ? kp.stage_copy * 4 : total;
     kp.zero_bytes = (kp.bulk_ok && !kp.pad_persist) ? total - c1 : 0;
   }
   h->step_mode = prm->reserved0;
@@ -462,10 +465,10 @@ extern "C" int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_d
 // latency and the kernel's prologue overlap the tail of whatever kernel precedes it on the stream; every kernel launched
 // through here executes griddepcontrol.wait before its first global-memory access.  CHS_NO_PDL=1 launches plainly (A/B runs).
 template <typename K, typename A>
-static void launch_pdl(const ChsHandle* h, K kernel, unsigned grid, unsigned threads, size_t smem, cudaStream_t st, const A& a) {
+static void launch_pdl(const ChsHandle* h, K kernel, dim3 grid, unsigned threads, size_t smem, cudaStream_t st, const A& a) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cfg.gridDim = grid; cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -476,10 +479,10 @@ static void launch_pdl(const ChsHandle* h, K kernel, unsigned grid, unsigned thr
 template <typename T> static void launch_step_variant(ChsHandle* h, const KArgs<T>& a, int grid, cudaStream_t st);
 #define CHS_LAUNCH(TT, MT, MB, FL)                                                                                 \
   do {                                                                                                               \
-    if (marl) { if (split) launch_pdl(h, step_kernel<TT, MT, MB, true, true, FL>, grid, h->threads, h->smem, st, a);  \
-                else launch_pdl(h, step_kernel<TT, MT, MB, true, false, FL>, grid, h->threads, h->smem, st, a); }     \
-    else      { if (split) launch_pdl(h, step_kernel<TT, MT, MB, false, true, FL>, grid, h->threads, h->smem, st, a); \
-                else launch_pdl(h, step_kernel<TT, MT, MB, false, false, FL>, grid, h->threads, h->smem, st, a); }    \
+    if (marl) { if (split) launch_pdl(h, step_kernel<TT, MT, MB, true, true, FL>, dim3(grid), h->threads, h->smem, st, a);  \
+                else launch_pdl(h, step_kernel<TT, MT, MB, true, false, FL>, dim3(grid), h->threads, h->smem, st, a); }     \
+    else      { if (split) launch_pdl(h, step_kernel<TT, MT, MB, false, true, FL>, dim3(grid), h->threads, h->smem, st, a); \
+                else launch_pdl(h, step_kernel<TT, MT, MB, false, false, FL>, dim3(grid), h->threads, h->smem, st, a); }    \
   } while (0)
 template <> void launch_step_variant<double>(ChsHandle* h, const KArgs<double>& a, int grid, cudaStream_t st) {
   const bool marl = h->kp.packing == CHS_PACK_MARL, split = a.p.split != 0;
@@ -513,7 +516,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
     if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
     const long long nthr = (long long)h->kp.D * h->E;
     if (h->kp.auto_reset && !h->knob_inline_reset) a.done_count = h->done_count;
-    launch_pdl(h, drone_kernel<T>, (unsigned)((nthr + 255) / 256), 256, 0, st, a);
+    launch_pdl(h, drone_kernel<T>, dim3((unsigned)((h->E + 255) / 256), (unsigned)h->kp.D), 256, 0, st, a);
     a.p.split = 1;
   }
   const bool defer = split && h->kp.auto_reset && !h->knob_inline_reset;
@@ -522,7 +525,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   if (defer) {
     KArgs<T> r = base_args<T>(h);
     r.done_list = h->done_list; r.done_count = h->done_count; r.obs = obs;
-    launch_pdl(h, reset_list_kernel<T>, 148 * 8, 256, 0, st, r);
+    launch_pdl(h, reset_list_kernel<T>, dim3(148 * 8), 256, 0, st, r);
   }
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;
@@ -574,7 +577,7 @@ static int launch_step_static(ChsHandle* h, unsigned char* scratch, const float*
   const bool defer = h->kp.auto_reset != 0;
   if (defer) a.done_count = count;
   const long long nthr = (long long)D * (long long)E;
-  launch_pdl(h, drone_kernel<T>, (unsigned)((nthr + 255) / 256), 256, 0, st, a);
+  launch_pdl(h, drone_kernel<T>, dim3((unsigned)((h->E + 255) / 256), (unsigned)h->kp.D), 256, 0, st, a);
   a.p.split = 1;
   if (defer) { a.done_list = list; a.done_count = count; }
   const int grid = (h->E + h->kp.G - 1) / h->kp.G;
@@ -582,7 +585,7 @@ static int launch_step_static(ChsHandle* h, unsigned char* scratch, const float*
   if (defer) {
     KArgs<T> r = base_args<T>(h);
     r.done_list = list; r.done_count = count; r.obs = obs;
-    launch_pdl(h, reset_list_kernel<T>, 148 * 8, 256, 0, st, r);
+    launch_pdl(h, reset_list_kernel<T>, dim3(148 * 8), 256, 0, st, r);
   }
   CUDA_TRY(cudaGetLastError());
   return CHS_OK;

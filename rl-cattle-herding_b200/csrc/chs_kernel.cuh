@@ -61,6 +61,14 @@ template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* ba
 
 __device__ __forceinline__ int ilog2_pow2(int g) { return 31 - __clz(g); }
 
+// (slot, row) = (it % n, it / n) of a flat item index without an integer division per item: `magic` = 2^32 / n + 1 is
+// exact for it < 2^22 and 2 <= n <= 32 (checked exhaustively); n == 1 passes the index through.
+__device__ __forceinline__ unsigned div_magic(int n) { return n > 1 ? 0xffffffffu / (unsigned)n + 1u : 0u; }
+__device__ __forceinline__ void split_item(int it, int n, unsigned magic, int& slot, int& row) {
+  row = (n == 1) ? it : (int)__umulhi((unsigned)it, magic);
+  slot = it - row * n;
+}
+
 // 16-byte asynchronous global->shared copy (LDGSTS); bytes past `src_bytes` (0..16) are zero-filled.
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -81,7 +89,7 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 // One env's observation image = staged rows followed by zero padding (from the CTA's zero block) up to R*L floats.
 __device__ __forceinline__ void bulk_copy_rows(const KParams& p, const float* stage_g, const float* zeros, float* dst) {
   const unsigned total = (unsigned)(p.R * p.L) * 4u;
-  unsigned c1 = (unsigned)p.stage_stride * 4u;
+  unsigned c1 = (unsigned)p.stage_copy * 4u;
   if (c1 > total) c1 = total;
   bulk_store(dst, stage_g, c1);
   if (total > c1 && !p.pad_persist) bulk_store(reinterpret_cast<char*>(dst) + c1, zeros, total - c1);
@@ -93,7 +101,7 @@ __device__ __forceinline__ void bulk_copy_rows(const KParams& p, const float* st
 // which is what bounds the host path (the stores cross PCIe) and the large batches (HBM).
 __device__ __forceinline__ void bulk_store_live(const KParams& p, const float* stage_g, float* dst) {
   const unsigned total = (unsigned)(p.R * p.L) * 4u;
-  unsigned c1 = (unsigned)p.stage_stride * 4u;
+  unsigned c1 = (unsigned)p.stage_copy * 4u;
   if (c1 > total) c1 = total;
   const char* src = reinterpret_cast<const char*>(stage_g);
   char* out = reinterpret_cast<char*>(dst);
@@ -130,7 +138,7 @@ __device__ __forceinline__ void copy_rows(const KParams& p, const float* stage_g
     const float4* src4 = reinterpret_cast<const float4*>(stage_g);
     float4* dst4 = reinterpret_cast<float4*>(dst);
     const int nq = RL >> 2;
-    const int sq = min(p.stage_stride >> 2, nq);
+    const int sq = min(p.stage_copy >> 2, nq);
     // staged part: two independent LDS -> STG pairs in flight per lane; zero padding: stores only
     int r = lane;
     for (; r + 32 < sq; r += 64) {
@@ -244,7 +252,7 @@ __device__ __forceinline__ void reset_envs(const KArgs<T>& a, Smem<T>& s, int e0
     }
     if (p.pad_persist) {
       // chs_reset is the one call that writes the caller-owned padding rows (ChsParams.persistent_padding)
-      const int q0 = p.stage_stride >> 2, nq = (p.R * p.L) >> 2;
+      const int q0 = p.stage_copy >> 2, nq = (p.R * p.L) >> 2;
       for (int it = t; it < nd * (nq - q0); it += nt) {
         const int g = s.dlist[it / (nq - q0)];
         reinterpret_cast<float4*>(a.obs + (size_t)(e0 + g) * p.R * p.L)[q0 + it % (nq - q0)] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -514,12 +522,12 @@ template <typename T>
 __global__ void __launch_bounds__(256) drone_kernel(const KArgs<T> a) {
   const KParams& p = a.p;
   const int E = p.E, D = p.D;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // grid = (ceil(E / 256), D): the drone slot is the block row, so no thread divides a flat index by E
+  const int e = blockIdx.x * blockDim.x + threadIdx.x, d = blockIdx.y;
   pdl_wait();
   pdl_launch_next();
-  if (idx == 0 && a.done_count) *a.done_count = 0;      // the list of finished envs is rebuilt by this step's step_kernel
-  if (idx >= (long long)D * E) return;
-  const int d = (int)(idx / E), e = (int)(idx - (long long)d * E);
+  if (e == 0 && d == 0 && a.done_count) *a.done_count = 0;      // the list of finished envs is rebuilt by this step's step_kernel
+  if (e >= E || d >= D) return;
   const int n = a.envi[e].z;
   if (d >= n) return;
   const T ctrl_dt = T(1.0) / T(p.ctrl_freq);
@@ -640,11 +648,12 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       // envs past the end of the batch are zero-filled through the src-size operand
       constexpr int EPC = 16 / (int)sizeof(V2);            // envs per 16-byte chunk
       const int cpr = G / EPC;                             // chunks per cow row
+      const int lcpr = ilog2_pow2(cpr);
       const int nchunk = 2 * M * cpr;
       if (sw >= 0) for (int it = sw; it < nchunk; it += snt) {
         const int arr = (it >= M * cpr) ? 1 : 0;
         const int r = it - arr * M * cpr;
-        const int j = r / cpr, c = r - j * cpr;
+        const int j = r >> lcpr, c = r & (cpr - 1);            // cpr is a power of two
         const int eb = e0 + c * EPC;
         int valid = E - eb; valid = valid < 0 ? 0 : (valid > EPC ? EPC : valid);
         const V2* src = (arr ? a.cvel : a.cpos) + (size_t)j * E + (valid > 0 ? eb : e0);
@@ -679,7 +688,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       }
       const unsigned m = __ballot_sync(0xffffffffu, fl);
       if (fl) s.flist[__popc(m & ((1u << t) - 1u))] = t;
-      if (t == 0) { s.misc[0] = __popc(m); s.misc[1] = 0; }
+      if (t == 0) { s.misc[0] = __popc(m); s.misc[1] = 0; s.misc[2] = (int)div_magic(__popc(m)); }
     }
     cp_async_wait_all();
   }
@@ -704,7 +713,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   const int ow = t - (nt - 32);             // lane index inside the last warp, < 0 elsewhere
   const bool obs_lane = (!FULL || p.bulk_ok) && a.obs != nullptr && ow >= 0 && ow < G && e0 + ow < E;
   if (obs_lane) {
-    const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_stride * 4u;
+    const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_copy * 4u;
     if (total > c1 && !p.pad_persist) {
       fence_async_smem();
       bulk_store(reinterpret_cast<char*>(a.obs + (size_t)(e0 + ow) * p.R * p.L) + c1, s.zeros, total - c1);
@@ -714,6 +723,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
 
   // ---------------- phase 1 ----------------
   const int nact = s.misc[0];
+  const unsigned nmagic = (unsigned)s.misc[2];
   if constexpr (SPLIT) {
     // the drones were integrated by drone_kernel: stage their positions and the own-state part of the obs rows
     if (t < ndt) {
@@ -818,7 +828,9 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         s.ccent[w] = make_double2(cx * inv_m, cy * inv_m);
       }
       for (int it = w; it < nact * M; it += nw) {
-        const int g = s.flist[it % nact], i = it / nact;
+        int slot, i;
+        split_item(it, nact, nmagic, slot, i);
+        const int g = s.flist[slot];
         T ux, uy;
         const unsigned* mw = a.amask ? a.amask + ((size_t)s.row[g] * M + i) * ((M + 31) >> 5) : nullptr;
         alpha_term<T>(s.cpos, s.cvel, i, g, G, M, mw, ux, uy);
@@ -837,7 +849,9 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     // non-reference kinematic herd: velocities first, then pos += vel * CTRL_TIMESTEP for
     // every cow of every env, then the herd centroid again; obs / reward / effectiveness below see the new positions
     for (int it = t; it < nact * M; it += nt) {
-      const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
+      int slot, i;
+      split_item(it, nact, nmagic, slot, i);
+      const int g = s.flist[slot], e = e0 + g;
       const auto ua = s.u[i * G + g];
       const auto v = herd_finish<T>(s.dpos, s.n[g], g, G, s.cpos[i * G + g], s.cvel[i * G + g], ua.x, ua.y);
       a.cvel[(size_t)i * E + e] = v;
@@ -896,7 +910,9 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   const int pw = t - pw0;               // < 0 on the drone warps when they are exempt
   if (!FULL || !p.cattle_integrate) {
     if (pw >= 0) for (int it = pw; it < nact * M; it += pnw) {
-      const int g = s.flist[it % nact], i = it / nact, e = e0 + g;
+      int slot, i;
+      split_item(it, nact, nmagic, slot, i);
+      const int g = s.flist[slot], e = e0 + g;
       const auto ua = s.u[i * G + g];
       const auto v = herd_finish<T>(s.dpos, s.n[g], g, G, s.cpos[i * G + g], s.cvel[i * G + g], ua.x, ua.y);
       a.cvel[(size_t)i * E + e] = v;       // positions are not advanced on the DYN path
@@ -918,7 +934,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   // In-kernel auto-reset rewrites the obs slot of a finished env with ordinary stores after the next barrier, so
   // there the issuing lane waits until its bulk write has landed (the wait overlaps phase 3 as well).
   if (obs_lane) {
-    const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_stride * 4u;
+    const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_copy * 4u;
     fence_async_smem();
     bulk_store_live(p, s.stage + (size_t)ow * p.stage_stride, a.obs + (size_t)(e0 + ow) * p.R * p.L);
     bulk_commit();
@@ -1188,7 +1204,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         float* trow = a.term_obs + (a.term_mode == 2 ? (size_t)s.termrow[t] : (size_t)e) * RL;
         if (p.pad_persist || p.dead_hi > p.dead_lo) {
           bulk_store_live(p, s.stage + (size_t)t * p.stage_stride, trow);
-          if (!p.pad_persist && p.zero_bytes > 0) bulk_store(reinterpret_cast<char*>(trow) + p.stage_stride * 4, s.zeros, (unsigned)p.zero_bytes);
+          if (!p.pad_persist && p.zero_bytes > 0) bulk_store(reinterpret_cast<char*>(trow) + p.stage_copy * 4, s.zeros, (unsigned)p.zero_bytes);
         } else {
           bulk_copy_rows(p, s.stage + (size_t)t * p.stage_stride, s.zeros, trow);
         }

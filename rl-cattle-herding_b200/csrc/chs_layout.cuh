@@ -37,7 +37,9 @@ struct KParams {
   int trunc_step_limit;  // truncated iff step_counter > this  (step_counter/CTRL_FREQ > EPISODE_LEN_SEC)
   int ctrl_freq;
   int env_id_offset;
-  int stage_stride;      // floats per env in the obs staging area (>= D*L, multiple of 4)
+  int stage_stride;      // floats per env in the obs staging area (>= D*L, multiple of 4, = 4 mod 8 so that the 32 envs of a
+                         // CTA spread over 8 banks instead of 2 or 4: lanes of a warp are consecutive envs)
+  int stage_copy;        // floats of an env's staged rows that leave for the obs image: D*L rounded up to 4
   int vec4_ok;           // (R*L) % 4 == 0 -> float4 copy-out
   int cattle_integrate;  // non-reference: herd positions advance by vel * CTRL_TIMESTEP every control step
   int aero_flags;        // bit0 drag, bit1 ground effect, bit2 downwash (chs_drone.cuh: dyn_substeps_aero)
@@ -45,7 +47,7 @@ struct KParams {
   int act4_ok;           // A == 4: one float4 load per action row
   int split;             // 1: drones are integrated by drone_kernel, step_kernel does the rest
   int bulk_ok;           // observations leave through bulk (TMA) stores: R*L*4 and the staging stride are multiples of 16 B
-  int zero_bytes;        // size of the shared zero block = R*L*4 - min(stage_stride*4, R*L*4)
+  int zero_bytes;        // size of the shared zero block = R*L*4 - min(stage_copy*4, R*L*4)
   int pad_persist;       // rows >= D of an obs image are caller-owned zeros: chs_step does not write them (ChsParams.persistent_padding)
   int dead_lo, dead_hi;  // columns [dead_lo, dead_hi) of every live obs row are caller-owned constant zeros (the unused neighbour
                          // slots, BaseRLAviary.py:313-314): not rewritten by chs_step when persistent_padding is on; 0, 0 = none
