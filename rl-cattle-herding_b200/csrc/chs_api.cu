@@ -65,6 +65,7 @@ struct ChsHandle {
   unsigned char* h_small;           // pinned mirror
   struct { const void* ptr; size_t bytes; } zeroed_host[4];   // pageable host buffers whose padding rows were zero-filled (chs_api_io.inc)
   unsigned zeroed_next;
+  bool knob_host_copy;              // CHS_HOST_COPY=1: the host path returns reward / flags / indices through its staging copy (A/B runs)
   bool knob_no_pdl;                 // CHS_NO_PDL=1: plain launches, no programmatic dependent launch
   bool knob_no_direct;              // CHS_NO_DIRECT=1: the host path stages through HBM even for pinned buffers
   int knob_smem_pad;
@@ -82,8 +83,13 @@ struct ChsHandle {
   int *d_count, *d_idx;
   bool obs_dst_is_host;             // set by chs_step_host around its launch: obs / terminal obs point into pinned host memory
   int* count_next;                  // host path: the ping-pong partner of the counter in use (zeroed by the launch)
+  int* d_cta_done;                  // host path: CTA ticket counter (chs_kernel.cuh: the last CTA publishes the finished-env count)
+  int* h_count;                     // host path: pinned word the kernel writes that count to; h_count_dev = its device alias
+  int* h_count_dev;
+  int* pub_cta_done;                // set by chs_step_host around its launch when the results go straight to pinned host arrays
+  int* pub_host_count;
   unsigned host_calls;
-  struct { const void* host; void* dev; } alias_cache[4];   // pinned host buffer -> device alias (chs_api_io.inc)
+  struct { const void* host; void* dev; } alias_cache[8];   // pinned host buffer -> device alias (chs_api_io.inc)
   unsigned alias_next;
 };
 
@@ -163,6 +169,7 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
 #undef CHS_SMEM_ATTR4
 #undef CHS_SMEM_ATTR
   h->kp.G = G;
+  h->kp.lay = h->f64 ? layout_for<double>(h->kp, G) : layout_for<float>(h->kp, G);
   h->kp.cp_ok = h->f64 ? 1 : ((G >= 2 && (h->E & 1) == 0) ? 1 : 0);
   h->threads = threads;
   h->smem = smem;
@@ -255,6 +262,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   h->knob_inline_reset = getenv("CHS_INLINE_RESET") != nullptr;
   h->knob_no_direct = getenv("CHS_NO_DIRECT") != nullptr;
   h->knob_no_pdl = getenv("CHS_NO_PDL") != nullptr;
+  h->knob_host_copy = getenv("CHS_HOST_COPY") != nullptr;
   kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
   kp.wrapper_quirks = (prm->marl_wrapper_quirks && prm->packing == CHS_PACK_MARL) ? 1 : 0;
@@ -330,9 +338,10 @@ extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
   void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->path, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count, h->amask,
-                  h->d_actions, h->d_obs, h->d_small, h->d_termobs, h->d_mask};
+                  h->d_actions, h->d_obs, h->d_small, h->d_termobs, h->d_mask, h->d_cta_done};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_small) cudaFreeHost(h->h_small);
+  if (h->h_count) cudaFreeHost(h->h_count);
   free(h);
   return CHS_OK;
 }
@@ -506,6 +515,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   a.actions = actions; a.obs = obs; a.reward = reward; a.terminated = term; a.truncated = trunc;
   a.term_obs = term_obs; a.term_mode = term_obs ? term_mode : 0; a.term_count = term_count; a.term_idx = term_idx;
   a.term_count_next = (term_obs && term_mode == 2) ? h->count_next : nullptr;
+  a.cta_done = h->pub_cta_done; a.host_count = h->pub_host_count;
   // dead-column skipping pays on the PCIe path only (fewer bytes per env); in HBM the extra, smaller bulk stores cost more
   // than the bytes they save (measured: 243 -> 294 us at 262 144 envs), so device destinations get the rows in one piece
   if (!h->obs_dst_is_host) a.p.dead_lo = a.p.dead_hi = 0;

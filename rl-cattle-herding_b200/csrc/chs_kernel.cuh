@@ -40,7 +40,7 @@ template <typename T> struct Smem {
 };
 
 template <typename T> __device__ __forceinline__ Smem<T> carve(unsigned char* base, const KParams& p) {
-  const SmemLayout l = smem_layout<T>(p.D, p.M, p.G, p.stage_stride, p.zero_bytes);
+  const SmemLayout& l = p.lay;
   Smem<T> s;
   s.dpos = reinterpret_cast<typename VT<T>::v4*>(base + l.off_dpos);
   s.redA = reinterpret_cast<typename VT<T>::v4*>(base + l.off_redA);
@@ -919,12 +919,28 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     }
   }
   CHS_STAMP(21);
-  if (pw >= 0) for (int it = pw; it < M * G; it += pnw) {
-    const int g = it & (G - 1);
+  if (pw >= 0 && pw < M * G) {
+    // winding numbers (evaluate_herding_effectiveness).  The thread stride pnw is a multiple of 32, hence of G: a thread sees
+    // the same env in every round, so it takes the bounding box of that env's drone polygon once and only walks the polygon
+    // for cows inside the box -- a point outside it has winding number zero.  A non-finite vertex disables the shortcut.
+    const int g = pw & (G - 1);
     const int n = s.n[g];
     if (n > 0) {
-      const auto c = s.cpos[it];
-      if (cow_inside<T>(s.dpos, n, g, G, c.x, c.y)) atomicAdd(&s.herd[g], 1);
+      T x0 = Mth<T>::inf(), y0 = Mth<T>::inf(), x1 = -Mth<T>::inf(), y1 = -Mth<T>::inf();
+      bool finite = true;
+#pragma unroll 1
+      for (int i = 0; i < n; ++i) {
+        const auto P = s.dpos[i * G + g];
+        x0 = Mth<T>::min(x0, P.x); x1 = Mth<T>::max(x1, P.x);
+        y0 = Mth<T>::min(y0, P.y); y1 = Mth<T>::max(y1, P.y);
+        finite = finite && (P.x == P.x) && (P.y == P.y);
+      }
+      if (!finite) { x0 = y0 = -Mth<T>::inf(); x1 = y1 = Mth<T>::inf(); }
+      for (int it = pw; it < M * G; it += pnw) {
+        const auto c = s.cpos[it];
+        const bool outside = (c.x < x0) || (c.x > x1) || (c.y < y0) || (c.y > y1);
+        if (!outside && cow_inside<T>(s.dpos, n, g, G, c.x, c.y)) atomicAdd(&s.herd[g], 1);
+      }
     }
   }
   CHS_STAMP(5);
@@ -1218,6 +1234,15 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   CHS_STAMP(9);
   __syncthreads();
   CHS_STAMP(10);
+  // Host path without a result copy (chs_step_host, pinned buffers): the CTA that passes here last hands the number of
+  // finished envs to the caller's pinned counter -- every CTA's additions to term_count precede its ticket.
+  if (a.host_count && t == 0) {
+    __threadfence();
+    if (atomicAdd(a.cta_done, 1) == (int)gridDim.x - 1) {
+      *a.host_count = *reinterpret_cast<volatile int*>(a.term_count);
+      *a.cta_done = 0;
+    }
+  }
 
   // ---------------- phase 4 ----------------
   const int nd = s.misc[1];

@@ -28,6 +28,11 @@ constexpr int CHS_STAT_ROWS = 1024;   // rows of the statistics accumulator (a p
 
 enum DroneField { F_A = 0, F_B, F_C, F_D, F_E, F_F, F_G, F_COUNT };
 
+// shared-memory carve-up of one CTA (byte offsets; smem_layout below), computed by the host for the launch shape in use
+struct SmemLayout {
+  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_ccent, off_ctab, off_zero, off_int, total;
+};
+
 struct KParams {
   int E, D, M, K, A, R, L;
   int act, packing, auto_reset;
@@ -54,6 +59,7 @@ struct KParams {
   int wrapper_quirks;    // MARL packing: outputs are those of the reference RLlib wrapper's second invocation (ChsParams.marl_wrapper_quirks)
   int early_ok;          // warp 0 may start its drone chain before the other warps finish staging (CHS_NO_EARLY=1 clears it)
   uint32_t seed_lo, seed_hi;
+  SmemLayout lay;        // = smem_layout<T>(D, M, G, stage_stride, zero_bytes): every thread of every CTA would recompute it otherwise
 };
 
 template <typename T> struct KArgs {
@@ -84,6 +90,8 @@ template <typename T> struct KArgs {
   int* term_count;                   // mode 2: atomic row counter
   int* term_idx;                     // mode 2: env index of each compact row
   int* term_count_next;              // mode 2, nullable: the counter the NEXT call will use; zeroed by this launch (ping-pong)
+  int* cta_done;                     // host path, nullable: ticket counter of the CTAs that finished phase 3 (device memory, 0 between launches)
+  int* host_count;                   // host path, nullable: pinned host word that receives *term_count from the last CTA
   const uint8_t* reset_mask;         // reset kernel only (nullable = all)
   int* done_list;                    // deferred reset (split mode): env ids finished this step (nullable = reset in the kernel)
   int* done_count;                   // number of entries, zeroed by drone_kernel
@@ -93,9 +101,6 @@ template <typename T> struct KArgs {
 };
 
 // ---- shared-memory carve-up (per CTA of G envs) ----------------------------------------------------
-struct SmemLayout {
-  int off_dpos, off_cpos, off_cvel, off_u, off_redA, off_redB, off_stage, off_ccent, off_ctab, off_zero, off_int, total;
-};
 
 template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, int M, int G, int stage_stride, int zero_bytes) {
   SmemLayout s;

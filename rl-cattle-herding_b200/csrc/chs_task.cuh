@@ -167,17 +167,35 @@ __device__ __forceinline__ void drone_cattle_coop(const KParams& p, bool valid, 
     const int nobs = (p.M < 16) ? p.M : 16;
     const int jend = want_reward ? p.M : nobs;
     const bool al8 = (p.L & 1) == 0;
-    for (int j = sub; j < jend; j += C) {
-      const auto c = s_cpos[j * G + g];
-      const T dx = c.x - me.x, dy = c.y - me.y;
-      if (j < nobs) {
-        const int col = cbase + 2 * j;
-        if (col + 1 < p.L) {
-          if (al8) *reinterpret_cast<float2*>(row + col) = make_float2((float)dx, (float)dy);
-          else { row[col] = (float)dx; row[col + 1] = (float)dy; }
-        } else if (col < p.L) { row[col] = (float)dx; }
+    if (al8 && cbase + 2 * nobs <= p.L) {
+      // the usual shape: every observed cow has both columns inside the row and the row is 8-byte aligned -- one float2 store
+      // per cow, no per-cow column tests; cows past the observed 16 only enter the minimum
+      float2* r2 = reinterpret_cast<float2*>(row + cbase);
+      int j = sub;
+      for (; j < nobs; j += C) {
+        const auto c = s_cpos[j * G + g];
+        const T dx = c.x - me.x, dy = c.y - me.y;
+        r2[j] = make_float2((float)dx, (float)dy);
+        m2 = Mth<T>::min(m2, dx * dx + dy * dy);
       }
-      m2 = Mth<T>::min(m2, dx * dx + dy * dy);
+      for (; j < jend; j += C) {
+        const auto c = s_cpos[j * G + g];
+        const T dx = c.x - me.x, dy = c.y - me.y;
+        m2 = Mth<T>::min(m2, dx * dx + dy * dy);
+      }
+    } else {
+      for (int j = sub; j < jend; j += C) {
+        const auto c = s_cpos[j * G + g];
+        const T dx = c.x - me.x, dy = c.y - me.y;
+        if (j < nobs) {
+          const int col = cbase + 2 * j;
+          if (col + 1 < p.L) {
+            if (al8) *reinterpret_cast<float2*>(row + col) = make_float2((float)dx, (float)dy);
+            else { row[col] = (float)dx; row[col + 1] = (float)dy; }
+          } else if (col < p.L) { row[col] = (float)dx; }
+        }
+        m2 = Mth<T>::min(m2, dx * dx + dy * dy);
+      }
     }
   }
   for (int o = C >> 1; o > 0; o >>= 1) {
