@@ -551,8 +551,8 @@ def run_cuda_arm(args):
                            "d2h_bytes_per_step": E * live + small + int(nterm / Ke * live),
                            "steps": Ke, "per_rank_d2h_gbs": (E * live + small + nterm / Ke * live) * Ke / float(e2e_s.item()) / 1e9,
                            "api": "CattleHerdingBatchedEnv.step_host (chs_step_host): the kernel reads the actions from, and writes "
-                                  "observations / terminal observations straight into, the caller's pinned buffers; reward, flags "
-                                  "and done indices return in one small copy; stream synchronised every step"}
+                                  "observations / terminal observations / reward / flags / done indices straight into, the caller's pinned "
+                                  "buffers (no staging, no copy node: one launch and one stream synchronisation per step)"}
     rot.close()
 
     # ---- BASELINE configs[2] and configs[3], same method, every rank ----
