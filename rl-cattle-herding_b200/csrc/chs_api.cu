@@ -502,7 +502,11 @@ template <> void launch_step_variant<float>(ChsHandle* h, const KArgs<float>& a,
   const bool big = (h->reg_variant == 2 && h->threads <= 256) || (h->reg_variant == 0 && h->threads <= 256 && (long long)grid * h->threads > 148LL * 512);
   const bool marl = h->kp.packing == CHS_PACK_MARL, split = a.p.split != 0;
   // lean build unless a runtime-checked feature is in use
-  const bool full = a.p.aero_flags || a.p.cattle_integrate || a.p.wrapper_quirks || !a.p.cp_ok || !a.p.bulk_ok || a.dbg_clock || h->knob_full;
+  const bool full = a.p.aero_flags || a.p.cattle_integrate || a.p.wrapper_quirks || !a.p.cp_ok || !a.p.bulk_ok || h->knob_full
+#ifndef CHS_PROFILE_LEAN
+                    || a.dbg_clock
+#endif
+      ;
   if (full) { if (big) CHS_LAUNCH(float, 256, 4, true); else CHS_LAUNCH(float, 512, 1, true); }
   else      { if (big) CHS_LAUNCH(float, 256, 4, false); else CHS_LAUNCH(float, 512, 1, false); }
 }

@@ -1,4 +1,5 @@
-"""Per-phase latency of the fused step kernel from in-kernel clock64() stamps (GPU box).
+"""Per-phase latency of the fused step kernel from in-kernel clock64() stamps (GPU box).  The stamps live in the FULL build;
+to time the lean build that ships, point CHS_LIB at a library compiled with -DCHS_PROFILE_LEAN.
     python tools/phase_timing.py [envs] [G] [threads] [drones] [cattle]"""
 import ctypes as C
 import os
