@@ -82,6 +82,70 @@ __device__ __forceinline__ void alpha_term(const typename VT<T>::v2* s_cpos, con
   uy = T(k::C2_ALPHA) * gy + T(k::C2_ALPHA) * cy;
 }
 
+// alpha_term for herds of more than 32 cows with the mask table: the first four mask words (up to 128 cows) are fetched
+// together, one L2 round trip instead of one per 32-cow chunk (the loads of the plain version are serialised by the walk over
+// each chunk's set bits).  Out of line on purpose: the small-herd kernels are sensitive to every instruction added to their
+// straight-line path (+2 % at 65 536 envs with this code inlined).
+template <typename T>
+__device__ __noinline__ void alpha_term_wide(const typename VT<T>::v2* s_cpos, const typename VT<T>::v2* s_cvel,
+                                             int i, int g, int G, int M, const unsigned* __restrict__ mwords, T* out) {
+  const auto qi = s_cpos[i * G + g];
+  const auto pi = s_cvel[i * G + g];
+  T gx = 0, gy = 0, cx = 0, cy = 0;
+  unsigned mk[4];
+  mk[0] = __ldg(mwords); mk[1] = __ldg(mwords + 1);
+  mk[2] = (M > 64) ? __ldg(mwords + 2) : 0u;
+  mk[3] = (M > 96) ? __ldg(mwords + 3) : 0u;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    unsigned mask = mk[c];
+    while (mask) {
+      const int j = c * 32 + __ffs(mask) - 1;
+      mask &= mask - 1;
+      const auto qj = s_cpos[j * G + g];
+      const auto pj = s_cvel[j * G + g];
+      lattice_term<T>(qj.x - qi.x, qj.y - qi.y, pj.x - pi.x, pj.y - pi.y, T(k::SIGMA_ALPHA), T(1.0 / k::SIGMA_ALPHA),
+                      gx, gy, cx, cy);
+    }
+  }
+  for (int j0 = 128; j0 < M; j0 += 32) {
+    unsigned mask = __ldg(mwords + (j0 >> 5));
+    while (mask) {
+      const int j = j0 + __ffs(mask) - 1;
+      mask &= mask - 1;
+      const auto qj = s_cpos[j * G + g];
+      const auto pj = s_cvel[j * G + g];
+      lattice_term<T>(qj.x - qi.x, qj.y - qi.y, pj.x - pi.x, pj.y - pi.y, T(k::SIGMA_ALPHA), T(1.0 / k::SIGMA_ALPHA),
+                      gx, gy, cx, cy);
+    }
+  }
+  out[0] = T(k::C2_ALPHA) * gx + T(k::C2_ALPHA) * cx;
+  out[1] = T(k::C2_ALPHA) * gy + T(k::C2_ALPHA) * cy;
+}
+
+// Herd centroid of the G envs of a CTA for herds of 48 cows and more: 8 lanes per env taken from the END of the worker range
+// (`wrev` = 0 on the last worker thread, `nw` worker threads, every one of them calls), cows strided over the lanes,
+// xor-shuffle tree.  Out of line for the same reason as alpha_term_wide.
+template <typename T>
+__device__ __noinline__ void centroid_wide(const typename VT<T>::v2* s_cpos, double2* s_ccent, int G, int M, int wrev, int nw) {
+  const double inv_m = 1.0 / (double)M;
+  for (int base = 0; base < 8 * G; base += nw) {
+    const int idx = base + wrev, g = idx >> 3, sub = idx & 7;
+    const bool live = idx < 8 * G;
+    double cx = 0, cy = 0;
+    if (live) {
+#pragma unroll 2
+      for (int j = sub; j < M; j += 8) { const auto c = s_cpos[j * G + g]; cx += (double)c.x; cy += (double)c.y; }
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+      cx += __shfl_xor_sync(0xffffffffu, cx, o);
+      cy += __shfl_xor_sync(0xffffffffu, cy, o);
+    }
+    if (live && sub == 0) s_ccent[g] = make_double2(cx * inv_m, cy * inv_m);
+  }
+}
+
 // shepherd (delta) interaction + predator repulsion + gamma term of cow i (flockUtils.py:271-323,343-348,
 // 150-160), then the velocity update and speed clip of BaseAviary.py:1384-1395.  `ua` is the alpha term.
 template <typename T>

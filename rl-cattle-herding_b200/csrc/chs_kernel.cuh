@@ -827,7 +827,14 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     const int nw = nt - wt0;
     if (t >= wt0) {
       const int w = t - wt0;
-      if (w < G) {
+      // Herd centroid per env (float64; phase 3 needs it).  Small herds: one thread per env, serial, in front of its alpha
+      // items.  Herds of 48 cows and more: AFTER the alpha items, 8 lanes per env taken from the END of the worker range
+      // (the threads with the fewest alpha items), cows strided over the lanes, xor-shuffle tree -- the serial 100-cow loop
+      // made the first G worker threads the last to reach the barrier (4000 cycles, measured with the lean-build stamps;
+      // config 3: 17.4 -> 16.2 us), while for 20 cows the tree costs more instructions than it saves latency.  Either way
+      // the summation order depends on M only, not on the launch shape or the step mode.
+      const bool wide_herd = M >= 48;
+      if (!wide_herd && w < G) {
         double cx = 0, cy = 0;
 #pragma unroll 4
         for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + w]; cx += (double)c.x; cy += (double)c.y; }
@@ -840,9 +847,11 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         const int g = s.flist[slot];
         T ux, uy;
         const unsigned* mw = a.amask ? a.amask + ((size_t)s.row[g] * M + i) * ((M + 31) >> 5) : nullptr;
-        alpha_term<T>(s.cpos, s.cvel, i, g, G, M, mw, ux, uy);
+        if (mw && M > 32) { T u2[2]; alpha_term_wide<T>(s.cpos, s.cvel, i, g, G, M, mw, u2); ux = u2[0]; uy = u2[1]; }
+        else alpha_term<T>(s.cpos, s.cvel, i, g, G, M, mw, ux, uy);
         s.u[i * G + g] = mk2<T>(ux, uy);
       }
+      if (wide_herd) centroid_wide<T>(s.cpos, s.ccent, G, M, nw - 1 - w, nw);
     }
   }
   CHS_STAMP(3);

@@ -201,3 +201,45 @@ def test_host_path_counts_and_terminal_rows_over_many_calls():
         assert np.array_equal(obs, ot.cpu().numpy()) and np.array_equal(term, tt.cpu().numpy()) and np.array_equal(trunc, ut.cpu().numpy())
     assert seen > 100
     env.close(); twin.close()
+
+
+@pytest.mark.parametrize("knob", ["CHS_NO_PDL", "CHS_HOST_COPY", "CHS_NO_DIRECT"])
+def test_launch_and_host_path_knobs_do_not_change_results(knob, monkeypatch):
+    """The step kernels are launched with programmatic dependent launch and the pinned host path is copy free; the knobs
+    that turn either off (plain launches / results through the staging copy / everything staged in HBM) are read at
+    chs_create and must give the same bits: device path against device path, host path against host path, 30 steps with
+    resets, fused and split."""
+    E = 700
+    rng = np.random.default_rng(5)
+    acts = [rng.uniform(-1, 1, (E, 3, 4)).astype(np.float32) for _ in range(30)]
+
+    def run(mode):
+        env = _make(E, step_mode=mode)
+        env.reset_host()
+        host, dev = [], []
+        for a in acts:
+            obs, rew, term, trunc, idx, tobs = env.step_host(a)
+            host.append((obs.copy(), rew.copy(), term.copy(), trunc.copy(), np.sort(idx.copy()),
+                         tobs[np.argsort(idx)].copy()))
+        twin = _make(E, step_mode=mode)
+        twin.reset()
+        for a in acts:
+            out = twin.step(torch.from_numpy(a).cuda())
+            dev.append(tuple(x.clone() for x in out) + (twin.terminal_obs.clone(),))
+        st = twin.get_state()
+        env.close(); twin.close()
+        return host, dev, st
+
+    for mode in ("fused", "split"):
+        monkeypatch.delenv(knob, raising=False)
+        ref = run(mode)
+        monkeypatch.setenv(knob, "1")
+        got = run(mode)
+        for t, (a, b) in enumerate(zip(ref[0], got[0])):
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y), (knob, mode, "host", t)
+        for t, (a, b) in enumerate(zip(ref[1], got[1])):
+            for x, y in zip(a, b):
+                assert torch.equal(x, y), (knob, mode, "device", t)
+        for k in ref[2]:
+            assert np.array_equal(ref[2][k], got[2][k], equal_nan=True), (knob, mode, k)
