@@ -201,6 +201,11 @@ class CattleHerdingBatchedEnv:
             }
             self._host_np = {k: v.numpy() for k, v in self._host.items()}
             self._n_done = C.c_int32(0)
+            # the argument list of chs_step_host never changes (the buffers are owned by this object): built once, so that a
+            # call costs one ctypes dispatch instead of ten pointer conversions
+            h = self._host
+            self._host_args = (self._h, _ptr(h["actions"]), _ptr(h["obs"]), _ptr(h["reward"]), _ptr(h["terminated"]),
+                               _ptr(h["truncated"]), C.byref(self._n_done), _ptr(h["done_idx"]), _ptr(h["terminal_obs"]))
         return self._host_np
 
     def reset_host(self, mask=None):
@@ -225,10 +230,9 @@ class CattleHerdingBatchedEnv:
         hb = self._host_buffers()
         if actions is not None and actions is not hb["actions"]:
             np.copyto(hb["actions"], np.asarray(actions, dtype=np.float32).reshape(hb["actions"].shape))
-        h = self._host
-        _lib.check(self.lib.chs_step_host(self._h, _ptr(h["actions"]), _ptr(h["obs"]), _ptr(h["reward"]),
-                                          _ptr(h["terminated"]), _ptr(h["truncated"]), C.byref(self._n_done),
-                                          _ptr(h["done_idx"]), _ptr(h["terminal_obs"]), self._stream()))
+        rc = self.lib.chs_step_host(*self._host_args, self._stream())
+        if rc:
+            _lib.check(rc)
         n = self._n_done.value
         return hb["obs"], hb["reward"], hb["terminated"], hb["truncated"], hb["done_idx"][:n], hb["terminal_obs"][:n]
 
