@@ -65,6 +65,7 @@ struct ChsHandle {
   unsigned char* h_small;           // pinned mirror
   struct { const void* ptr; size_t bytes; } zeroed_host[4];   // pageable host buffers whose padding rows were zero-filled (chs_api_io.inc)
   unsigned zeroed_next;
+  bool knob_early_rows;             // CHS_EARLY_ROWS=1: the host path stores the live rows before phase 3, finished envs included (A/B runs)
   bool knob_host_copy;              // CHS_HOST_COPY=1: the host path returns reward / flags / indices through its staging copy (A/B runs)
   bool knob_no_pdl;                 // CHS_NO_PDL=1: plain launches, no programmatic dependent launch
   bool knob_no_direct;              // CHS_NO_DIRECT=1: the host path stages through HBM even for pinned buffers
@@ -263,6 +264,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   h->knob_no_direct = getenv("CHS_NO_DIRECT") != nullptr;
   h->knob_no_pdl = getenv("CHS_NO_PDL") != nullptr;
   h->knob_host_copy = getenv("CHS_HOST_COPY") != nullptr;
+  h->knob_early_rows = getenv("CHS_EARLY_ROWS") != nullptr;
   kp.split = 0;
   kp.cattle_integrate = prm->cattle_integrate ? 1 : 0;
   kp.wrapper_quirks = (prm->marl_wrapper_quirks && prm->packing == CHS_PACK_MARL) ? 1 : 0;
@@ -523,6 +525,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   // dead-column skipping pays on the PCIe path only (fewer bytes per env); in HBM the extra, smaller bulk stores cost more
   // than the bytes they save (measured: 243 -> 294 us at 262 144 envs), so device destinations get the rows in one piece
   if (!h->obs_dst_is_host) a.p.dead_lo = a.p.dead_hi = 0;
+  a.p.late_rows = (h->obs_dst_is_host && h->kp.auto_reset && obs && !h->knob_early_rows) ? 1 : 0;
   const int grid = (h->E + h->kp.G - 1) / h->kp.G;
   // split mode: the drones get their own barrier-free kernel; auto picks it once the batch is several waves deep
   const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 1024);

@@ -203,7 +203,7 @@ def test_host_path_counts_and_terminal_rows_over_many_calls():
     env.close(); twin.close()
 
 
-@pytest.mark.parametrize("knob", ["CHS_NO_PDL", "CHS_HOST_COPY", "CHS_NO_DIRECT"])
+@pytest.mark.parametrize("knob", ["CHS_NO_PDL", "CHS_HOST_COPY", "CHS_NO_DIRECT", "CHS_EARLY_ROWS"])
 def test_launch_and_host_path_knobs_do_not_change_results(knob, monkeypatch):
     """The step kernels are launched with programmatic dependent launch and the pinned host path is copy free; the knobs
     that turn either off (plain launches / results through the staging copy / everything staged in HBM) are read at
