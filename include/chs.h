@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define CHS_ABI_VERSION 4
+#define CHS_ABI_VERSION 4   /* 4: ChsStateView.active_agents / path_len, ChsParams.marl_wrapper_quirks, chs_stats slots 11-15 */
 #define CHS_MAX_DRONES 12   /* GLOBAL_MAX_NUM_DRONES, BaseAviary.py:112 */
 #define CHS_NUM_STATS 16
 #define CHS_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)   /* size of the static device array behind chs_step_static_scratch */
@@ -199,14 +199,18 @@ int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, float* rewa
 int chs_step_static_scratch(ChsHandle* h, const float* actions_dev, float* obs_dev, float* reward_dev,
                             uint8_t* terminated_dev, uint8_t* truncated_dev, float* terminal_obs_dev, void* stream);
 
-/* Same step with HOST buffers (what a numpy-facing VecEnv calls): actions are copied H2D from
- * the handle's pinned staging area, results D2H, and the call returns after the stream has
- * drained.  Terminal observations come back compacted: *n_done_host envs finished, their indices
- * are in done_idx_host[0..n) (capacity E) and their terminal observations in
- * terminal_obs_host[i][R][L] (capacity E rows); both may be NULL.
- * Observation rows >= max_drones are identically zero, so only the first max_drones rows of every image cross
- * PCIe; the padding rows of obs_host / terminal_obs_host are zero-filled by the library the first time it sees a
- * buffer (by address) and are not rewritten afterwards -- do not scribble on them. */
+/* Same step with HOST buffers (what a numpy-facing VecEnv calls); the call returns after the stream has drained.
+ * Terminal observations come back compacted: *n_done_host envs finished, their indices are in done_idx_host[0..n)
+ * (capacity E) and their terminal observations in terminal_obs_host[i][R][L] (capacity E rows); all three may be NULL.
+ * PINNED (page-locked, mapped) buffers are used in place: the kernel reads the actions from actions_host and stores
+ * observations, terminal observations, reward, flags and done indices straight into the caller's arrays over PCIe; the
+ * finished-env count arrives through a pinned word of the handle.  Nothing is staged and no copy is enqueued: one launch
+ * and one stream synchronisation per call.  If any of the buffers is pageable the call takes the staged path (device staging
+ * + copies; actions are copied from the caller's array) with the same results.
+ * Observation rows >= max_drones are identically zero, so only the first max_drones rows of every image cross PCIe (under
+ * ChsParams.persistent_padding also without the dead neighbour columns): the padding of obs_host / terminal_obs_host is
+ * written by chs_reset_host (staged path: zero-filled the first time a buffer address is seen) and is not rewritten
+ * afterwards -- do not scribble on it. */
 int chs_step_host(ChsHandle* h, const float* actions_host, float* obs_host, float* reward_host,
                   uint8_t* terminated_host, uint8_t* truncated_host, int32_t* n_done_host,
                   int32_t* done_idx_host, float* terminal_obs_host, void* stream);
