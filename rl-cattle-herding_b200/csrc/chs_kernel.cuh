@@ -401,20 +401,24 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
     a.path[(size_t)d * E + e] = T(-1);
   }
   if (a.obs == nullptr || !(parts & RESET_OBS)) return;
+  // Lane l holds the spawn position of drone l (line / two-row spawn, BaseAviary.py:251-277); whoever needs another drone's
+  // position takes it from that lane with a shuffle.  A rebuild costs ~2000 warp instructions and reset_list_kernel is bound
+  // by instruction issue (as many instructions per step as drone_kernel at 7 % finished envs), so nothing is recomputed.
+  T sx = T(0), sy = T(0);
+  if (lane < n) spawn_xy<T>(lane, n, sx, sy);
   // two nearest other drones of drone `lane` (strict '<' keeps index order on ties, like drone_neighbors)
   int j1 = -1, j2 = -1;
-  if (lane < n) {
-    T mx, my;
-    spawn_xy<T>(lane, n, mx, my);
+  {
     T d1 = Mth<T>::inf(), d2 = Mth<T>::inf();
     CHS_COLD_LOOP for (int j = 0; j < n; ++j) {
-      if (j == lane) continue;
-      T ox, oy;
-      spawn_xy<T>(j, n, ox, oy);
-      const T dx = ox - mx, dy = oy - my;
-      const T dist = Mth<T>::sqrt(dx * dx + dy * dy);
-      if (dist < d1) { d2 = d1; j2 = j1; d1 = dist; j1 = j; }
-      else if (dist < d2) { d2 = dist; j2 = j; }
+      const T ox = __shfl_sync(full, sx, j), oy = __shfl_sync(full, sy, j);
+      const T dx = ox - sx, dy = oy - sy;
+      const T dist = (j == lane || lane >= n) ? Mth<T>::inf() : Mth<T>::sqrt(dx * dx + dy * dy);
+      const bool lt1 = dist < d1, lt2 = dist < d2;
+      d2 = lt1 ? d1 : (lt2 ? dist : d2);
+      j2 = lt1 ? j1 : (lt2 ? j : j2);
+      d1 = lt1 ? dist : d1;
+      j1 = lt1 ? j : j1;
     }
   }
   float* ob = a.obs + (size_t)e * RL;
@@ -423,21 +427,17 @@ __device__ __forceinline__ void reset_env_warp(const KArgs<T>& a, int e, int n, 
   const bool cow_ok = (lane >> 1) < nobs;
   if (cow_ok) { const auto xy = srow[lane >> 1]; cow_c = (lane & 1) ? xy.y : xy.x; }
   CHS_COLD_LOOP for (int d = 0; d < n && d < p.R; ++d) {
-    T mx, my;
-    spawn_xy<T>(d, n, mx, my);
+    const T mx = __shfl_sync(full, sx, d), my = __shfl_sync(full, sy, d);
     const int nb1 = __shfl_sync(full, j1, d), nb2 = __shfl_sync(full, j2, d);
+    // columns 0..31, one per lane: z | zeros | the two neighbour slots (columns 10..13) | zeros
+    const int nbl = (lane < 12) ? nb1 : nb2;
+    const T ox = __shfl_sync(full, sx, nbl >= 0 ? nbl : 0), oy = __shfl_sync(full, sy, nbl >= 0 ? nbl : 0);
+    float v = 0.f;
+    if (lane == 0) v = (float)T(k::TARGET_ALT);
+    else if (lane >= 10 && lane < 14 && nbl >= 0) v = (lane & 1) ? (float)(oy - my) : (float)(ox - mx);
     float* orow = ob + d * L;
-    {   // columns 0 .. cbase-1: z, zeros, two neighbour slots, zeros (cbase <= 34: two passes at most)
-      CHS_COLD_LOOP for (int c = lane; c < cbase; c += 32) {
-        float v = 0.f;
-        if (c == 0) v = (float)T(k::TARGET_ALT);
-        else if (c >= 10 && c < 14) {
-          const int nb = (c < 12) ? nb1 : nb2;
-          if (nb >= 0) { T ox, oy; spawn_xy<T>(nb, n, ox, oy); v = (c & 1) ? (float)(oy - my) : (float)(ox - mx); }
-        }
-        orow[c] = v;
-      }
-    }
+    if (lane < cbase) orow[lane] = v;
+    if (32 + lane < cbase) orow[32 + lane] = 0.f;                        // sb3 packing: columns 32, 33 (cbase <= 34)
     if (cbase + lane < L) orow[cbase + lane] = cow_ok ? (float)(cow_c - ((lane & 1) ? my : mx)) : 0.f;
     CHS_COLD_LOOP for (int c = cbase + 32 + lane; c < L; c += 32) orow[c] = 0.f;
   }
