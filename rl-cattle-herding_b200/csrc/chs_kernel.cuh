@@ -972,6 +972,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   }
 
   // ---------------- phase 3 ----------------
+  // Hand-off: warp 0 releases the other warps into the rebuild of the finished envs as soon as it knows which envs finished
+  // (bar.arrive, below), and goes on with the statistics, the env scalars and the terminal observations while they work:
+  // the rebuild is the tail of every CTA that holds a finished env, and the part of phase 3 behind the flags is a third of it.
+  const bool handoff = !SPLIT && (!FULL || p.bulk_ok) && nt >= 64;
   if (t < 32) {
     bool fin = false;
     const int e = e0 + t;
@@ -1158,6 +1162,24 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       st_bad = !(r_global == r_global) || fabs(r_global) == Mth<double>::inf();
       done_env = fin && p.auto_reset;          // the observation of this step goes to term_obs, a fresh one to obs
     }
+    // what the rebuild of a finished env needs (in-kernel rebuild only: in split mode reset_list_kernel does all of this)
+    int new_n = 0, new_row = 0;
+    const bool rebuild = active && done_env && !a.done_list;
+    if (rebuild) {
+      new_n = draw_num_drones(p, p.env_id_offset + e, ej.z + 1);
+      new_row = ei.w + 1;                      // Cattle_Spawn_Index pre-increment with wrap (BaseAviary.py:600-603)
+      if (new_row >= p.n_sims) new_row = 0;
+      s.newn[t] = new_n; s.row[t] = new_row; s.epi[t] = ej.z + 1; s.done[t] = 1;
+    }
+    {
+      const unsigned m = __ballot_sync(0xffffffffu, rebuild);
+      if (rebuild) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
+      if (t == 0) s.misc[1] = __popc(m);
+    }
+    if (handoff) {
+      __threadfence_block();
+      asm volatile("bar.arrive 0, %0;" ::"r"(nt) : "memory");
+    }
     // ---- episode statistics: fire-and-forget reductions (RED, no return value, nothing waits on them) into the row of the
     // [CHS_STAT_ROWS][CHS_NUM_STATS] accumulator picked by the CTA index, so that the thousands of envs that finish in one
     // step of a large batch do not queue on sixteen addresses; chs_stats sums the rows.
@@ -1215,11 +1237,8 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         fin = false;
       } else if (done_env) {
         ej.z += 1;
-        nn = draw_num_drones(p, p.env_id_offset + e, ej.z);
-        row = ei.w + 1;
-        if (row >= p.n_sims) row = 0;
+        nn = new_n; row = new_row;
         sc = 0; scA = 0; epret = 0;
-        s.newn[t] = nn; s.row[t] = row; s.epi[t] = ej.z;
       } else {
         fin = false;
       }
@@ -1242,12 +1261,11 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         bulk_commit();
       }
     }
-    const unsigned m = __ballot_sync(0xffffffffu, fin);
-    if (fin) s.dlist[__popc(m & ((1u << t) - 1u))] = t;
-    if (t == 0) { s.misc[1] = __popc(m); if (blockIdx.x == 0) { atomicAdd(a.stats + 10, (double)E); if (a.term_count_next) *a.term_count_next = 0; } }
+    if (t == 0 && blockIdx.x == 0) { atomicAdd(a.stats + 10, (double)E); if (a.term_count_next) *a.term_count_next = 0; }
   }
   CHS_STAMP(9);
-  __syncthreads();
+  if (!handoff) __syncthreads();
+  else if (t >= 32) asm volatile("bar.sync 0, %0;" ::"r"(nt) : "memory");      // warp 0 arrived at the hand-off
   CHS_STAMP(10);
   // Pinned-host destination (`late_rows`): the live rows leave only now, and not at all for the envs that finished -- their
   // slot receives the first observation of the next episode from the rebuild, and every byte saved is a byte less on PCIe
@@ -1289,14 +1307,41 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     // (finished env, part) items over the warps, straight to global memory: no shared-memory staging.  The obs slot of a
     // finished env already received this step's live rows through a bulk store of the last warp; that write has to
     // land before the ordinary stores of the new episode's first observation (CTAs without a finished env skip this).
-    if (obs_lane) bulk_wait_all();
-    __syncthreads();
     const int warp = t >> 5, lane = t & 31, nwarp = nt >> 5;
-    for (int i = warp; i < 3 * nd; i += nwarp) {
-      const int g = s.dlist[i / 3], part = 1 << (i % 3);
-      PidPre<T> pid;
-      if (part == RESET_DRONES) pid = reset_preload<T>(a, e0 + g, lane);
-      reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, part, pid);
+    if (!handoff) {
+      if (obs_lane) bulk_wait_all();
+      __syncthreads();
+      for (int i = warp; i < 3 * nd; i += nwarp) {
+        const int g = s.dlist[i / 3], part = 1 << (i % 3);
+        PidPre<T> pid;
+        if (part == RESET_DRONES) pid = reset_preload<T>(a, e0 + g, lane);
+        reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, part, pid);
+      }
+    } else {
+      // Observation parts first: to the warps from the top down, never to warp 0 -- they follow the wait for the early write
+      // of the same slot, which is a barrier among warps 1.. only (warp 0 is still busy with the rest of phase 3).  Cow and
+      // drone parts: item j to warp j + 1, warp 0 last.  With one finished env the three parts run on three warps at once.
+      if (warp > 0) {
+        if (obs_lane) bulk_wait_all();
+        asm volatile("bar.sync 2, %0;" ::"r"(nt - 32) : "memory");
+        for (int k = nwarp - 1 - warp; k < nd; k += nwarp - 1) {
+          const int g = s.dlist[k];
+          PidPre<T> pid;
+          pid.e = pid.f = pid.g = mk4<T>(0, 0, 0, 0);
+          reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, RESET_OBS, pid);
+        }
+      }
+      for (int j = (warp + nwarp - 1) % nwarp; j < 2 * nd; j += nwarp) {
+        const int g = s.dlist[j >> 1];
+        PidPre<T> pid;
+        pid.e = pid.f = pid.g = mk4<T>(0, 0, 0, 0);
+        if (j & 1) {
+          pid = reset_preload<T>(a, e0 + g, lane);
+          reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, RESET_DRONES, pid);
+        } else {
+          reset_env_warp<T>(a, e0 + g, s.newn[g], s.row[g], s.epi[g], lane, RESET_COWS, pid);
+        }
+      }
     }
   }
   if (!FULL || p.bulk_ok) bulk_wait_read();       // shared memory must outlive the pending bulk reads
