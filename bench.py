@@ -442,7 +442,10 @@ def run_cuda_arm(args):
     # ---- headline: BASELINE configs[1] ----
     rot = Rotating(pkg, torch, dev, E, N, M, args.ctrl_freq, rank * E, packing=args.packing)
     if args.launch == "auto":
-        cands = [(8, 128), (16, 256), (8, 96), (4, 64), (4, 128), (16, 128)] if E <= 16384 else [(32, 256), (16, 256), (16, 128)]
+        # (28, T): wave-fitted shapes -- a CTA handles 28 of its 32 env slots, so that 4096 envs make 147 CTAs for the 148 SMs
+        # (one CTA of 512 threads per SM) and 16 384 envs make 586 CTAs for the 592 resident slots of the 64-register build
+        cands = ([(8, 128), (16, 256), (8, 96), (4, 64), (4, 128), (16, 128), (32, 512), (28, 512), (28, 256)] if E <= 16384
+                 else [(32, 256), (16, 256), (16, 128)])
         modes = ("fused", "split") if args.step_mode == "auto" and E > 16384 else (("fused",) if args.step_mode == "auto" else (args.step_mode,))
         tuned = rot.autotune(cands, modes)
     else:
@@ -567,7 +570,7 @@ def run_cuda_arm(args):
                             [(4, 256), (2, 128), (2, 256), (4, 128)], ("fused",), peak, peak_src, "8d100c_1024env")
         Ec4 = 65536 // world
         c4 = measure_config(pkg, torch, dist, dev, rank, Ec4, 3, 20, args.ctrl_freq, min(K, 100), W,
-                            [(32, 256), (16, 256)] if Ec4 > 16384 else [(16, 256), (8, 128), (16, 128)],
+                            [(32, 256), (16, 256)] if Ec4 > 16384 else [(16, 256), (8, 128), (16, 128), (28, 256), (32, 256), (28, 512)],
                             ("fused", "split") if Ec4 >= 16384 else ("fused",), peak, peak_src, f"3d20c_{Ec4}env")
         c4["scaling"] = "strong: 65 536 envs in total, split evenly by env index"
         if rank == 0:
@@ -580,7 +583,7 @@ def run_cuda_arm(args):
             if Es == E:
                 continue
             r = measure_config(pkg, torch, None, dev, 0, Es, N, M, args.ctrl_freq, 60, W,
-                               [(16, 256), (32, 256), (16, 128)], ("fused", "split"), peak, peak_src, f"{N}d{M}c_{Es}env")
+                               [(16, 256), (32, 256), (28, 256), (16, 128)], ("fused", "split"), peak, peak_src, f"{N}d{M}c_{Es}env")
             sweep.append({"envs": Es, "ms_per_step": r["ms_per_step"], "env_steps_per_s": r["env_steps_per_s"],
                           "hbm_frac": r["roofline"]["frac"], "hbm_frac_compact": r["roofline"]["compact"]["frac"],
                           "launch": r["launch"], "batches_rotated": r["batches_rotated"]})

@@ -262,8 +262,10 @@ int chs_set_phase_clock(ChsHandle* h, int64_t* clock_dev);
  * NCCL once per training iteration. */
 int chs_stats(ChsHandle* h, double* stats_host, int32_t reset);
 
-/* Launch-shape override after creation (bench autotuning): envs per CTA (1,2,4,8,16,32) and threads
- * per CTA (multiple of 32, <= 1024). */
+/* Launch-shape override after creation (bench autotuning): envs per CTA (1..32: a power of two, or any even count --
+ * the CTA then keeps the next power of two as its shared-memory stride and leaves the other slots empty, which lets the
+ * grid be fitted to whole waves of the 148 SMs, e.g. 28 envs x 147 CTAs for 4096 envs) and threads per CTA (multiple of
+ * 32, 32..512).  Results do not depend on the shape. */
 int chs_set_launch(ChsHandle* h, int32_t envs_per_block, int32_t threads_per_block);
 
 #ifdef __cplusplus

@@ -146,8 +146,13 @@ static int smem_for(const ChsHandle* h, int G) {
 
 static const int kSmemCap = 200 * 1024;
 
-static int configure_launch(ChsHandle* h, int G, int threads) {
-  if (G < 1 || G > 32 || (G & (G - 1))) return fail(CHS_ERR_INVALID, "envs_per_block must be a power of two in 1..32");
+static int configure_launch(ChsHandle* h, int gact, int threads) {
+  // envs_per_block need not be a power of two: the shared-memory arrays keep a power-of-two stride G >= gact and the CTA
+  // leaves the slots beyond gact empty.  An even count keeps the 16-byte async herd copies aligned.
+  if (gact < 1 || gact > 32) return fail(CHS_ERR_INVALID, "envs_per_block must be in 1..32");
+  int G = 1;
+  while (G < gact) G <<= 1;
+  if (gact != G && (gact & 1)) return fail(CHS_ERR_INVALID, "envs_per_block must be a power of two or even");
   if (threads < 32 || threads > 512 || (threads & 31)) return fail(CHS_ERR_INVALID, "threads_per_block must be a multiple of 32 in 32..512");
   int smem = smem_for(h, G);
   smem += h->knob_smem_pad;
@@ -170,6 +175,7 @@ static int configure_launch(ChsHandle* h, int G, int threads) {
 #undef CHS_SMEM_ATTR4
 #undef CHS_SMEM_ATTR
   h->kp.G = G;
+  h->kp.gact = gact;
   h->kp.lay = h->f64 ? layout_for<double>(h->kp, G) : layout_for<float>(h->kp, G);
   h->kp.cp_ok = h->f64 ? 1 : ((G >= 2 && (h->E & 1) == 0) ? 1 : 0);
   h->threads = threads;
@@ -354,7 +360,7 @@ extern "C" int chs_get_dims(const ChsHandle* h, ChsDims* out) {
   out->action_width = h->kp.A; out->obs_rows = h->kp.R; out->obs_len = h->kp.L;
   out->substeps = h->kp.K; out->action_buffer_size = (int)(0.15 * h->kp.ctrl_freq);
   out->reward_width = reward_width(h); out->flag_width = flag_width(h);
-  out->envs_per_block = h->kp.G; out->threads_per_block = h->threads; out->smem_bytes = h->smem;
+  out->envs_per_block = h->kp.gact; out->threads_per_block = h->threads; out->smem_bytes = h->smem;
   return CHS_OK;
 }
 
@@ -526,7 +532,7 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   // than the bytes they save (measured: 243 -> 294 us at 262 144 envs), so device destinations get the rows in one piece
   if (!h->obs_dst_is_host) a.p.dead_lo = a.p.dead_hi = 0;
   a.p.late_rows = (h->obs_dst_is_host && h->kp.auto_reset && obs && !h->knob_early_rows) ? 1 : 0;
-  const int grid = (h->E + h->kp.G - 1) / h->kp.G;
+  const int grid = (h->E + h->kp.gact - 1) / h->kp.gact;
   // split mode: the drones get their own barrier-free kernel; auto picks it once the batch is several waves deep
   const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 1024);
   if (split) {
@@ -597,7 +603,7 @@ static int launch_step_static(ChsHandle* h, unsigned char* scratch, const float*
   launch_pdl(h, drone_kernel<T>, dim3((unsigned)((h->E + 255) / 256), (unsigned)h->kp.D), 256, 0, st, a);
   a.p.split = 1;
   if (defer) { a.done_list = list; a.done_count = count; }
-  const int grid = (h->E + h->kp.G - 1) / h->kp.G;
+  const int grid = (h->E + h->kp.gact - 1) / h->kp.gact;
   launch_step_variant<T>(h, a, grid, st);
   if (defer) {
     KArgs<T> r = base_args<T>(h);

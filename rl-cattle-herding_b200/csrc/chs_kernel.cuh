@@ -578,7 +578,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   Smem<T> s = carve<T>(smem_raw, p);
   const int t = threadIdx.x, nt = blockDim.x, G = p.G, E = p.E, D = p.D, M = p.M;
   const int lg = ilog2_pow2(G);
-  const int e0 = blockIdx.x * G;
+  // A CTA handles `gact` <= G consecutive envs; G stays the power-of-two stride of the shared-memory arrays (slots >= gact
+  // are treated like envs past the end of the batch).  The host picks gact so that the grid fills whole waves of the 148 SMs.
+  const int e0 = blockIdx.x * p.gact;
+  const int Ev = (e0 + p.gact < E) ? e0 + p.gact : E;      // end of this CTA's envs
   const T ctrl_dt = T(1.0) / T(p.ctrl_freq);
   const T pyb_dt = T(1.0) / T(p.ctrl_freq * p.K);
   const int DG = D * G;
@@ -618,7 +621,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   int4 pre_i = make_int4(0, 0, 0, 0), pre_j = make_int4(0, 0, 0, 0);
   double2 pre_f = make_double2(0.0, 0.0);
   double pre_ret = 0.0;
-  const bool env_lane = (t < G) && (e0 + t < E);      // warp 0 only (G <= 32)
+  const bool env_lane = (t < G) && (e0 + t < Ev);     // warp 0 only (G <= 32)
   if (env_lane) {
     // env scalars are fetched once, here, and stay in registers until phase 3
     const int e = e0 + t;
@@ -628,7 +631,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   float act0[4] = {0.f, 0.f, 0.f, 0.f};
   typename VT<T>::v4 sp0 = mk4<T>(0, 0, 0, 0), sp1 = sp0, sp2 = sp0;     // split mode: fields A, C and the own2 row
   T path0 = T(0);                                                        // running path length of the first drone item
-  const bool have0 = (t < ndt) && (t < DG) && (e0 + (t & (G - 1)) < E);
+  const bool have0 = (t < ndt) && (t < DG) && (e0 + (t & (G - 1)) < Ev);
   if constexpr (SPLIT) {
     if (have0) {
       const int g = t & (G - 1), d = t >> lg, e = e0 + g;
@@ -662,7 +665,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
         const int r = it - arr * M * cpr;
         const int j = r >> lcpr, c = r & (cpr - 1);            // cpr is a power of two
         const int eb = e0 + c * EPC;
-        int valid = E - eb; valid = valid < 0 ? 0 : (valid > EPC ? EPC : valid);
+        int valid = Ev - eb; valid = valid < 0 ? 0 : (valid > EPC ? EPC : valid);
         const V2* src = (arr ? a.cvel : a.cpos) + (size_t)j * E + (valid > 0 ? eb : e0);
         V2* dst = (arr ? s.cvel : s.cpos) + j * G + c * EPC;
         cp_async16(dst, src, valid * (int)sizeof(V2));
@@ -672,7 +675,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       const size_t st = (size_t)D * E;
       for (int it = t; it < DG; it += nt) {
         const int g = it & (G - 1), d = it >> lg, e = e0 + g;
-        if (e < E) s.redA[it] = a.drone[F_A * st + (size_t)d * E + e];
+        if (e < Ev) s.redA[it] = a.drone[F_A * st + (size_t)d * E + e];
       }
     }
     // curriculum table: 76 chunks of 16 bytes
@@ -682,7 +685,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     if (FULL && !p.cp_ok) {
       for (int it = t; it < M * G; it += nt) {
         const int g = it & (G - 1), j = it >> lg, e = e0 + g;
-        if (e < E) { s.cpos[it] = a.cpos[(size_t)j * E + e]; s.cvel[it] = a.cvel[(size_t)j * E + e]; }
+        if (e < Ev) { s.cpos[it] = a.cpos[(size_t)j * E + e]; s.cvel[it] = a.cvel[(size_t)j * E + e]; }
         else { s.cpos[it] = mk2<T>(0, 0); s.cvel[it] = mk2<T>(0, 0); }
       }
     }
@@ -718,7 +721,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   // finished env's image goes to term_obs instead (phase 3 sends both pieces there) and its obs slot receives the
   // first observation of the next episode, whose rows >= D are zeros as well.
   const int ow = t - (nt - 32);             // lane index inside the last warp, < 0 elsewhere
-  const bool obs_lane = (!FULL || p.bulk_ok) && a.obs != nullptr && ow >= 0 && ow < G && e0 + ow < E;
+  const bool obs_lane = (!FULL || p.bulk_ok) && a.obs != nullptr && ow >= 0 && ow < G && e0 + ow < Ev;
   if (obs_lane) {
     const unsigned total = (unsigned)(p.R * p.L) * 4u, c1 = (unsigned)p.stage_copy * 4u;
     if (total > c1 && !p.pad_persist) {
@@ -736,7 +739,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     if (t < ndt) {
       for (int it = t; it < DG; it += ndt) {
         const int g = it & (G - 1), d = it >> lg, e = e0 + g;
-        if (e < E && d < s.n[g]) {
+        if (e < Ev && d < s.n[g]) {
           typename VT<T>::v4 A = sp0, C = sp1, O = sp2;
           T pl = path0;
           if (it != t) {
@@ -764,7 +767,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     T held_pl = T(0);
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
-      if (e < E && d < s.n[g]) {
+      if (e < Ev && d < s.n[g]) {
         DroneState<T> ds;
         float act[4];
         T pl = path0;
@@ -876,7 +879,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     __syncthreads();
     for (int it = t; it < M * G; it += nt) {
       const int g = it & (G - 1), j = it >> lg, e = e0 + g;
-      if (e < E) {
+      if (e < Ev) {
         const auto c = s.cpos[it];
         const auto v = s.cvel[it];
         const auto nc = mk2<T>(c.x + v.x * ctrl_dt, c.y + v.y * ctrl_dt);
@@ -896,7 +899,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     for (int it = t; it < DG; it += ndt) {
       const int g = it & (G - 1), d = it >> lg, e = e0 + g;
       const int n = s.n[g];
-      if (e < E && d < n)
+      if (e < Ev && d < n)
         drone_neighbors<T>(p, s.ctab, g, d, n, s.level[g], true, s.dpos, s.redA, s.redB, s.stage,
                            a.dbg_neighbors ? a.dbg_neighbors + ((size_t)e * D + d) * 2 : nullptr,
                            (CHS_STAMPS_ON && a.dbg_clock && t == 0) ? a.dbg_clock + (size_t)blockIdx.x * 32 + 24 : nullptr);
@@ -914,7 +917,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     for (int base = 0; base < items; base += nt) {
       const int idx = base + tb, it = idx >> lc, sub = idx & (C - 1);
       const int g = it & (G - 1), d = it >> lg;
-      const bool valid = idx < items && e0 + g < E && d < s.n[g];
+      const bool valid = idx < items && e0 + g < Ev && d < s.n[g];
       drone_cattle_coop<T>(p, valid, g, d, sub, C, true, s.dpos, s.cpos, s.redB, s.stage);
     }
   }
@@ -979,7 +982,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   if (t < 32) {
     bool fin = false;
     const int e = e0 + t;
-    const bool active = (t < G && e < E);
+    const bool active = (t < G && e < Ev);
     // values that cross the warp-converged statistics block below
     int4 ej = pre_j;
     double2 ef = pre_f;
@@ -1292,7 +1295,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
     const size_t RL = (size_t)p.R * p.L;
     for (int g = warp; g < G; g += nwarp) {
       const int e = e0 + g;
-      if (e >= E) break;
+      if (e >= Ev) break;
       float* dst = a.obs ? a.obs + (size_t)e * RL : nullptr;
       if (s.done[g]) {
         dst = nullptr;

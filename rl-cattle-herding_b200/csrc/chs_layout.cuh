@@ -58,6 +58,7 @@ struct KParams {
                          // slots, BaseRLAviary.py:313-314): not rewritten by chs_step when persistent_padding is on; 0, 0 = none
   int wrapper_quirks;    // MARL packing: outputs are those of the reference RLlib wrapper's second invocation (ChsParams.marl_wrapper_quirks)
   int late_rows;         // observations go to pinned host memory: live rows are stored after phase 3, finished envs skipped
+  int gact;              // envs a CTA of the step kernel handles (<= G, the power-of-two shared-memory stride): wave fitting
   int early_ok;          // warp 0 may start its drone chain before the other warps finish staging (CHS_NO_EARLY=1 clears it)
   uint32_t seed_lo, seed_hi;
   SmemLayout lay;        // = smem_layout<T>(D, M, G, stage_stride, zero_bytes): every thread of every CTA would recompute it otherwise

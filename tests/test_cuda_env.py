@@ -132,11 +132,12 @@ def test_host_path_equals_device_path():
 
 
 def test_results_do_not_depend_on_launch_shape_or_sharding():
-    """Same env ids => same results for every CTA shape, and for 1 shard of 96 envs vs 3 shards of 32
-    (the multi-GPU sharding rule, exercised on one GPU)."""
+    """Same env ids => same results for every CTA shape -- including the wave-fitted ones, where a CTA handles a
+    non-power-of-two number of envs and leaves the rest of its power-of-two slots empty -- and for 1 shard of 96 envs vs 3
+    shards of 32 (the multi-GPU sharding rule, exercised on one GPU)."""
     E = 96
     ref, _ = _make(E, envs_per_block=8, threads_per_block=128)
-    variants = [_make(E, envs_per_block=g, threads_per_block=th)[0] for g, th in ((2, 64), (4, 256), (32, 128), (16, 512))]
+    variants = [_make(E, envs_per_block=g, threads_per_block=th)[0] for g, th in ((2, 64), (4, 256), (32, 128), (16, 512), (28, 512), (6, 96), (14, 256))]
     # one env per CTA cannot stage the herd with 16-byte async copies and runs the full build of the kernel: another
     # compilation of the same source, equal up to fp32 contraction (like the register variants below)
     other_build = _make(E, envs_per_block=1, threads_per_block=64)[0]

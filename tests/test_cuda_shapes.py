@@ -20,7 +20,8 @@ pytestmark = pytest.mark.gpu
 import subset_check as sc  # noqa: E402  (tests/_golden.py put oracle/ on sys.path)
 
 # bench.py's candidate list for the 4096-env headline (run_cuda_arm: `cands`)
-BENCH_SHAPES = [(4, 64), (8, 96)] + [(g, th) for g in (4, 8, 16, 32) for th in (128, 256)]
+# (28, 512), (28, 256): wave-fitted shapes -- a CTA handles 28 of its 32 env slots, 147 CTAs on the 148 SMs at 4096 envs
+BENCH_SHAPES = [(4, 64), (8, 96), (32, 512), (28, 512), (28, 256)] + [(g, th) for g in (4, 8, 16, 32) for th in (128, 256)]
 
 
 def _make(E, N=3, M=20, rows=100, **kw):
@@ -73,10 +74,12 @@ def test_sweep_points_auto_mode_subset_vs_oracle(E):
 
 @pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("mode", ["fused", "split"])
-def test_register_variants_and_modes_vs_oracle(variant, mode):
-    """Both register budgets of the fp32 kernel in both step modes, 8192 envs, against the oracle (not a sibling)."""
+@pytest.mark.parametrize("G", [16, 28])
+def test_register_variants_and_modes_vs_oracle(variant, mode, G):
+    """Both register budgets of the fp32 kernel in both step modes, 8192 envs, against the oracle (not a sibling); G = 28
+    is the wave-fitted shape of the large batches (a ragged last CTA: 8192 = 292 x 28 + 16)."""
     import rl_cattle_herding_b200 as pkg
-    env, table = _make(8192, step_mode=mode, envs_per_block=16, threads_per_block=256)
+    env, table = _make(8192, step_mode=mode, envs_per_block=G, threads_per_block=256)
     pkg._lib.check(env.lib.chs_set_register_variant(env._h, variant))
     env.reset()
     chk = _run(env, table, sc.subset_ids(8192, 16, 8), 12, 3, warm=10)
