@@ -55,6 +55,12 @@ class CattleHerdingBatchedEnv:
                  marl_wrapper_quirks=False):
         if not torch.cuda.is_available():
             raise RuntimeError("CattleHerdingBatchedEnv needs a CUDA device (there is no CPU fallback)")
+        self._ctor = dict(num_envs=num_envs, num_drones=num_drones, num_cattle=num_cattle, pyb_freq=pyb_freq, ctrl_freq=ctrl_freq,
+                          act=act, start_level=start_level, fixed_num_drones=fixed_num_drones, obs_rows=obs_rows,
+                          auto_reset=auto_reset, precision=precision, device=device, env_id_offset=env_id_offset, seed=seed,
+                          packing=packing, aero=aero, cattle_integrate=cattle_integrate, step_mode=step_mode,
+                          persistent_padding=persistent_padding, marl_wrapper_quirks=marl_wrapper_quirks)
+        self._spawn_table = None
         self.lib = _lib.load()
         self.device = torch.device("cuda", torch.cuda.current_device() if device is None else
                                    (device if isinstance(device, int) else torch.device(device).index or 0))
@@ -129,9 +135,66 @@ class CattleHerdingBatchedEnv:
     def set_launch(self, envs_per_block, threads_per_block):
         _lib.check(self.lib.chs_set_launch(self._h, int(envs_per_block), int(threads_per_block)))
 
+    # launch shapes `autotune_launch` tries by default: (envs per CTA, threads per CTA).  28 = wave fitting (include/chs.h,
+    # chs_set_launch): 147 CTAs for the 148 SMs at 4096 envs, 586 for the 592 resident slots at 16 384
+    LAUNCH_CANDIDATES = ((2, 128), (4, 64), (4, 128), (4, 256), (8, 128), (8, 256), (16, 128), (16, 256), (28, 256), (32, 256),
+                         (28, 512), (32, 512))
+
+    def autotune_launch(self, candidates=None, modes=None, steps=24):
+        """Picks the launch shape (and, when `modes` names several, the step mode) that steps a batch like this one fastest
+        on this GPU, and applies it to this env.  The timing runs on a PROBE env built from the same constructor arguments
+        (same batch size, spawn table and seeds; destroyed afterwards), so this env's state, episode counters and statistics
+        are untouched: every candidate steps the probe 8 + `steps` times under uniform random actions between CUDA events
+        on the current stream, and the two best are measured again, interleaved.  Results do not depend on the shape
+        (tests/test_cuda_env.py), only the time does -- the best shape depends on how the batch fills whole waves of the
+        148 SMs.  Returns (ms per step, envs per CTA, threads per CTA, mode)."""
+        if self._spawn_table is None:
+            raise RuntimeError("set_spawn_table() first: the probe steps real episodes")
+        cands = list(candidates or self.LAUNCH_CANDIDATES)
+        modes = list(modes or [self._ctor["step_mode"]])
+        probe = CattleHerdingBatchedEnv(spawn_table=self._spawn_table, **self._ctor)
+        try:
+            act = [torch.rand((self.num_envs, self.max_drones, self.action_width), device=self.device) * 2 - 1 for _ in range(4)]
+            probe.reset()
+
+            def timed(g, th, mode, n):
+                probe.set_launch(g, th)
+                probe.set_step_mode(mode)
+                for i in range(8):
+                    probe.step(act[i % 4], want_terminal_obs=False)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for i in range(n):
+                    probe.step(act[i % 4], want_terminal_obs=False)
+                e1.record()
+                e1.synchronize()
+                return e0.elapsed_time(e1) / n
+
+            ranked = []
+            for mode in modes:
+                for g, th in cands:
+                    try:
+                        ranked.append((timed(g, th, mode, steps), g, th, mode))
+                    except RuntimeError:        # shape refused for this batch (shared memory, occupancy variant)
+                        continue
+            if not ranked:
+                raise RuntimeError("no launch candidate was accepted")
+            ranked.sort()
+            again = {r[1:]: [] for r in ranked[:2]}
+            for _ in range(3):
+                for key in again:
+                    again[key].append(timed(*key, steps))
+            best = min((float(np.median(v)),) + k for k, v in again.items())
+        finally:
+            probe.close()
+        self.set_launch(best[1], best[2])
+        self.set_step_mode(best[3])
+        return best
+
     def set_spawn_table(self, table):
         t = np.ascontiguousarray(np.asarray(table, dtype=np.float64))
         assert t.ndim == 3 and t.shape[2] == 2, "spawn table must be (n_sims, cows_per_sim, 2)"
+        self._spawn_table = t
         _lib.check(self.lib.chs_set_spawn_table(self._h, t.ctypes.data_as(C.c_void_p), t.shape[0], t.shape[1]))
 
     def enable_debug_outputs(self):

@@ -72,10 +72,11 @@ def action_space(num_drones, width):
 class GpuCattleVecEnv(_VecEnvBase):
     def __init__(self, num_envs, num_drones=12, num_cattle=16, physics=Physics.DYN, pyb_freq=240, ctrl_freq=60,
                  obs=ObservationType.COKIN, act=ActionType.VEL, gui=False, record=False, device=None, seed=0,
-                 spawn_table=None, **sim_kwargs):
+                 spawn_table=None, autotune_launch=False, **sim_kwargs):
         """kwargs follow `CattleAviary.__init__` (sb3_envs/CattleAviary.py:14-28) with its defaults for
         frequencies; `physics` must be Physics.DYN (Bullet's PYB solver is not reproducible and not provided);
-        `gui` / `record` are refused: there is no graphics stack."""
+        `gui` / `record` are refused: there is no graphics stack.  `autotune_launch=True` times the launch shapes of
+        `CattleHerdingBatchedEnv.LAUNCH_CANDIDATES` on a probe batch once and keeps the fastest (results are unaffected)."""
         if physics != Physics.DYN:
             raise ValueError("only Physics.DYN is implemented (the PYB constraint solver is not available)")
         if gui or record:
@@ -88,6 +89,8 @@ class GpuCattleVecEnv(_VecEnvBase):
         self.sim = CattleHerdingBatchedEnv(num_envs, num_drones=num_drones, num_cattle=num_cattle, pyb_freq=pyb_freq,
                                            ctrl_freq=ctrl_freq, act=act, auto_reset=True, spawn_table=spawn_table,
                                            device=device, seed=seed, **sim_kwargs)
+        if autotune_launch:
+            self.sim.autotune_launch()
         super().__init__(num_envs, observation_space(self.sim.obs_rows, self.sim.obs_len),
                          action_space(self.sim.max_drones, self.sim.action_width))
         self.CTRL_FREQ, self.PYB_FREQ = int(ctrl_freq), int(pyb_freq)

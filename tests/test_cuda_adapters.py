@@ -13,7 +13,8 @@ import cattle_oracle as co  # noqa: E402
 def test_vec_env_contract():
     import rl_cattle_herding_b200 as pkg
     E = 64
-    venv = pkg.GpuCattleVecEnv(E, num_drones=3, num_cattle=20, ctrl_freq=30, fixed_num_drones=3, device=0, seed=2)
+    venv = pkg.GpuCattleVecEnv(E, num_drones=3, num_cattle=20, ctrl_freq=30, fixed_num_drones=3, device=0, seed=2,
+                               autotune_launch=True)      # the tuned launch shape must not change a single bit
     twin = pkg.CattleHerdingBatchedEnv(E, num_drones=3, num_cattle=20, ctrl_freq=30, fixed_num_drones=3, device=0, seed=2,
                                        spawn_table=pkg.spawn.generate(100, 20, seed=0))
     assert venv.num_envs == E and venv.observation_space.shape == (12, 66) and venv.action_space.shape == (3, 4)

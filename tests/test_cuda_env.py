@@ -255,3 +255,26 @@ def test_free_running_fp32_vs_oracle_uniform_actions():
             env.reset(mask=m.cuda()); sync(redo); episodes += len(redo)
     assert episodes >= 10 and worst < 1e-3, (episodes, worst)
     env.close()
+
+
+def test_autotune_launch_picks_a_shape_and_changes_no_result():
+    """`autotune_launch` times a probe env and only changes this env's launch shape: state, counters and statistics are
+    untouched, and what it steps afterwards equals an untuned env with the same seeds bit for bit."""
+    E = 2048
+    tuned, _ = _make(E)
+    tuned.reset()
+    cands = [(8, 128), (16, 256), (14, 256), (28, 512)]
+    best = tuned.autotune_launch(candidates=cands, steps=8)
+    assert (best[1], best[2]) in cands and best[0] > 0 and best[3] == "auto"
+    assert tuned.dims["envs_per_block"] == best[1] and tuned.dims["threads_per_block"] == best[2]
+    assert tuned.stats()[10] == 0
+    plain, _ = _make(E, envs_per_block=8, threads_per_block=128)
+    plain.reset()
+    assert torch.equal(tuned.obs, plain.obs)
+    gen = torch.Generator("cuda").manual_seed(3)
+    for t in range(6):
+        act = torch.rand((E, 3, 4), device="cuda", generator=gen) * 2 - 1
+        a, b = tuned.step(act), plain.step(act)
+        for x, y in zip(a, b):
+            assert torch.equal(x, y), t
+    tuned.close(); plain.close()
