@@ -326,16 +326,19 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
     err = cudaMemcpy(h->tab, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice);
     if (err != cudaSuccess) { chs_destroy(h); return fail(CHS_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(err)); }
   }
-  // launch shape: enough CTAs to cover the 148 SMs a few times over, shared memory permitting
+  // launch shape: the largest power-of-two group that still gives every one of the 148 SMs a CTA, shared memory permitting,
+  // with 256 threads -- (16, 256) at 3 drones / 20 cattle x 4096 envs, (4, 256) at 8 / 100 x 1024, (32, 256) from 4736 envs
+  // up: the best power-of-two shapes measured.  The wave-fitted shapes (28 envs per CTA) are a few per cent
+  // better still where the batch is about one wave; the Python layer's autotune_launch() finds them.
   int G = prm->envs_per_block, threads = prm->threads_per_block;
   if (G == 0) {
     G = 32;
     // not below two envs per CTA when that fits: one env per CTA cannot stage the herd with 16-byte async copies and
     // falls to the full build of the kernel (same results up to fp32 contraction, but not bit for bit)
-    while (G > 2 && (smem_for(h, G) > 64 * 1024 || (num_envs + G - 1) / G < 2 * 148)) G >>= 1;
+    while (G > 2 && (smem_for(h, G) > 64 * 1024 || (num_envs + G - 1) / G < 148)) G >>= 1;
     if (G == 2 && (num_envs < 2 || smem_for(h, 2) > 64 * 1024)) G = 1;
   }
-  if (threads == 0) threads = (G * kp.M <= 256) ? 128 : 256;
+  if (threads == 0) threads = (G * (kp.D + kp.M) < 128) ? 128 : 256;
   int rc = configure_launch(h, G, threads);
   if (rc != CHS_OK) { chs_destroy(h); return rc; }
   *out = h;
