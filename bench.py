@@ -384,11 +384,11 @@ def roofline_block(N, M, dims, E, ms, mode, peak, peak_src, traffic_key):
             "compact": {"bytes_per_env_step": compact, "achieved": ach_c, "frac": ach_c / peak},
             "peak_source": peak_src, "kernel_ms": ms,
             "kernel": "chs::step_kernel<float> (one launch per control step)" if mode == "fused" else
-                      "chs::drone_kernel<float> + chs::step_kernel<float, SPLIT> (+ chs::reset_list_kernel<float>): one control step"}
+                      "chs::drone_kernel<float> + chs::step_kernel<float, SPLIT>: one control step"}
 
 
 def launches_per_step(mode):
-    return 1 if mode == "fused" else 3
+    return 1 if mode == "fused" else 2
 
 
 def measure_config(pkg, torch, dist, dev, rank, E, N, M, ctrl_freq, K, W, cands, modes, peak, peak_src, key):

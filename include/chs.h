@@ -174,7 +174,7 @@ int chs_set_spawn_table(ChsHandle* h, const double* xy_host, int32_t n_sims, int
 int chs_reset(ChsHandle* h, const uint8_t* env_mask_dev, float* obs_dev, void* stream);
 
 /* BaseAviary.step (:335-465): one control step of every env.  Step mode 1 (fused) is ONE kernel launch; step mode 2
- * (split, picked automatically for batches several waves deep) is drone_kernel + step_kernel + reset_list_kernel, plus one
+ * (split, picked automatically for batches several waves deep) is drone_kernel + step_kernel, plus one
  * device-to-device copy when the downwash model is on (see chs_set_step_mode).
  * terminal_obs_dev (nullable): [E][R][L]; with auto_reset the pre-reset observation of each
  * finished env is written there (rows of other envs are left untouched) and obs_dev receives the
@@ -184,7 +184,7 @@ int chs_step(ChsHandle* h, const float* actions_dev, float* obs_dev, float* rewa
 
 /* No counterpart in the reference: added for callers that may not call cudaMalloc
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same control step, same arguments and same
- * results as chs_step in split mode (step mode 2: drone_kernel, step_kernel, reset_list_kernel), but the scratch those
+ * results as chs_step in split mode (here in its three-kernel form: drone_kernel, step_kernel, reset_list_kernel), but the scratch those
  * kernels hand data through -- the per-drone (ang_v, yaw) rows between the first two and the list of finished envs between
  * the last two -- lives in ONE file-scope `static __device__` array of CHS_STATIC_SCRATCH_BYTES (8 MiB) per GPU instead of
  * buffers from cudaMalloc.  Every GPU that loads the library holds that array until the process exits.  The call itself

@@ -60,7 +60,7 @@ struct ChsHandle {
   int step_mode;      // 0 auto, 1 fused (one kernel), 2 split (drone_kernel + step_kernel)
   // experiment knobs, read from the environment once at creation (tools/residency_probe.py and A/B runs):
   // CHS_SMEM_PAD=<bytes> extra dynamic shared memory per CTA, CHS_NO_BULK=1 warp copy-out instead of bulk stores,
-  // CHS_FULL_KERNEL=1 never use the lean build, CHS_INLINE_RESET=1 reset inside step_kernel in split mode too
+  // CHS_FULL_KERNEL=1 never use the lean build, CHS_DEFERRED_RESET=1 split mode lists finished envs and rebuilds them in reset_list_kernel (A/B runs)
   unsigned char* d_small;           // host path: count | reward | flags | done idx in one block (chs_api_io.inc)
   unsigned char* h_small;           // pinned mirror
   struct { const void* ptr; size_t bytes; } zeroed_host[4];   // pageable host buffers whose padding rows were zero-filled (chs_api_io.inc)
@@ -70,7 +70,7 @@ struct ChsHandle {
   bool knob_no_pdl;                 // CHS_NO_PDL=1: plain launches, no programmatic dependent launch
   bool knob_no_direct;              // CHS_NO_DIRECT=1: the host path stages through HBM even for pinned buffers
   int knob_smem_pad;
-  bool knob_full, knob_inline_reset;
+  bool knob_full, knob_deferred_reset;
   int *dbg_nb, *dbg_herd;
   long long* dbg_clock;
   int threads, smem;
@@ -266,7 +266,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   { const char* v = getenv("CHS_SMEM_PAD"); h->knob_smem_pad = v ? atoi(v) : 0; }
   h->knob_full = getenv("CHS_FULL_KERNEL") != nullptr;
   kp.early_ok = getenv("CHS_NO_EARLY") ? 0 : 1;
-  h->knob_inline_reset = getenv("CHS_INLINE_RESET") != nullptr;
+  h->knob_deferred_reset = getenv("CHS_DEFERRED_RESET") != nullptr;
   h->knob_no_direct = getenv("CHS_NO_DIRECT") != nullptr;
   h->knob_no_pdl = getenv("CHS_NO_PDL") != nullptr;
   h->knob_host_copy = getenv("CHS_HOST_COPY") != nullptr;
@@ -541,11 +541,15 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   if (split) {
     if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
     const long long nthr = (long long)h->kp.D * h->E;
-    if (h->kp.auto_reset && !h->knob_inline_reset) a.done_count = h->done_count;
+    if (h->kp.auto_reset && h->knob_deferred_reset) a.done_count = h->done_count;
     launch_pdl(h, drone_kernel<T>, dim3((unsigned)((h->E + 255) / 256), (unsigned)h->kp.D), 256, 0, st, a);
     a.p.split = 1;
   }
-  const bool defer = split && h->kp.auto_reset && !h->knob_inline_reset;
+  // Finished envs are rebuilt inside step_kernel in both modes (phase 5, on the warps that idle while warp 0 finishes phase
+  // 3).  Split mode used to list them and rebuild them in a third kernel, which was faster while the rebuild was 2000 cold
+  // instructions on the tail of a CTA; since the rebuild was trimmed the third kernel only costs (262 144 envs: 253.8 us
+  // deferred, 238.9 us in place; 65 536 envs: 73.4 / 69.4).  chs_step_static_scratch keeps the deferred form.
+  const bool defer = split && h->kp.auto_reset && h->knob_deferred_reset;
   if (defer) { a.done_list = h->done_list; a.done_count = h->done_count; }
   launch_step_variant<T>(h, a, grid, st);
   if (defer) {
