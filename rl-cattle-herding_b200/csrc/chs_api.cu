@@ -536,8 +536,10 @@ static int launch_step(ChsHandle* h, const float* actions, float* obs, float* re
   if (!h->obs_dst_is_host) a.p.dead_lo = a.p.dead_hi = 0;
   a.p.late_rows = (h->obs_dst_is_host && h->kp.auto_reset && obs && !h->knob_early_rows) ? 1 : 0;
   const int grid = (h->E + h->kp.gact - 1) / h->kp.gact;
-  // split mode: the drones get their own barrier-free kernel; auto picks it once the batch is several waves deep
-  const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 1024);
+  // split mode: the drones get their own barrier-free kernel; auto picks it once the fused grid would be more than about one
+  // wave of resident CTAs (measured at 3 drones / 20 cattle: 16 384 envs 23.5 us fused / 25.9 split, 24 576 envs 38.3 / 36.5,
+  // 49 152 envs 61.4 / 51.7)
+  const bool split = h->step_mode == 2 || (h->step_mode == 0 && (long long)h->E * h->kp.D >= 148LL * 448);
   if (split) {
     if (h->pos0) CUDA_TRY(cudaMemcpyAsync(h->pos0, h->drone, (size_t)h->kp.D * h->E * 4 * h->tsz, cudaMemcpyDeviceToDevice, st));
     const long long nthr = (long long)h->kp.D * h->E;

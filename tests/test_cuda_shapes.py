@@ -57,9 +57,9 @@ def test_4096_envs_every_bench_launch_shape(shape, mode):
     env.close()
 
 
-@pytest.mark.parametrize("E", [4096, 65536, 262144])
+@pytest.mark.parametrize("E", [4096, 24576, 65536, 262144])
 def test_sweep_points_auto_mode_subset_vs_oracle(E):
-    """The sweep points of bench.py in step_mode="auto" (fused up to 49 151 envs at 3 drones, split beyond): 16 steps,
+    """The sweep points of bench.py in step_mode="auto" (fused up to 22 100 envs at 3 drones, split beyond): 16 steps,
     256 envs on every step, resets included."""
     env, table = _make(E)
     env.reset()

@@ -2,7 +2,7 @@
 them (rotating batches larger than L2, one CUDA graph of K steps, one event pair), for the library named by CHS_LIB.
     CHS_LIB=/path/libchs_variant.so python tools/ab_bench.py [head] [c3] [mid] [c4] [big]
 Launch shapes: the ones bench.py's autotune settles on (fixed here so that variants are compared like for like) unless
-AB_SHAPES="G,T;G,T" overrides the launch shapes of every case named, AB_MODE=fused|split the step mode."""
+AB_SHAPES="G,T;G,T" overrides the launch shapes of every case named, AB_MODE=fused|split the step mode, AB_ENVS the batch size."""
 import os
 import sys
 
@@ -24,6 +24,7 @@ tag = os.path.basename(os.environ.get("CHS_LIB", "libchs.so"))
 for name in what:
     E, N, M, shapes, mode = CASES[name]
     mode = os.environ.get("AB_MODE", mode)
+    E = int(os.environ.get("AB_ENVS", E))
     if os.environ.get("AB_SHAPES"):
         shapes = [tuple(int(x) for x in s.split(",")) for s in os.environ["AB_SHAPES"].split(";")]
     rot = bench.Rotating(pkg, torch, dev, E, N, M, 30, 0)
