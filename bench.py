@@ -276,25 +276,40 @@ class Rotating:
         torch.cuda.synchronize()
         return s.elapsed_time(e) / n
 
+    def time_graph(self, n):
+        """n steps captured as one CUDA graph (the way the timed region runs them), replayed once untimed and once between
+        an event pair; ms per step.  Shapes that differ by 1-2 % are not separable by eager launches from Python."""
+        torch = self.torch
+        g = self.capture(n)
+        g.replay()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        g.replay()
+        e.record()
+        torch.cuda.synchronize()
+        self.graph = None
+        return s.elapsed_time(e) / n
+
     def autotune(self, candidates, modes, reps=48):
-        """Untimed: picks (envs per CTA, threads per CTA, step mode) by back-to-back stream time; the two best are
-        measured again, interleaved.  Returns (ms, G, threads, mode)."""
+        """Untimed: picks (envs per CTA, threads per CTA, step mode) by the time of a CUDA graph of `reps` steps; the three
+        best are measured again, interleaved.  Returns (ms, G, threads, mode)."""
+        reps = max(self.R, (reps // self.R) * self.R)          # whole rounds over the rotating batches
         ranked = []
         for mode in modes:
             for g, th in candidates:
                 try:
                     self.configure(g, th, mode)
                     self.run(2 * self.R)
-                    ranked.append((self.time_stream(reps), g, th, mode))
+                    ranked.append((self.time_graph(reps), g, th, mode))
                 except RuntimeError:
                     continue
         ranked.sort()
-        acc = {f[1:]: [] for f in ranked[:2]}
+        acc = {f[1:]: [] for f in ranked[:3]}
         for _ in range(3):
             for key in acc:
                 self.configure(*key)
                 self.run(self.R)
-                acc[key].append(self.time_stream(reps))
+                acc[key].append(self.time_graph(reps))
         best = min((float(np.median(v)), k[0], k[1], k[2]) for k, v in acc.items())
         self.configure(best[1], best[2], best[3])
         return best

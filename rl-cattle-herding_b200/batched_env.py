@@ -144,8 +144,8 @@ class CattleHerdingBatchedEnv:
         """Picks the launch shape (and, when `modes` names several, the step mode) that steps a batch like this one fastest
         on this GPU, and applies it to this env.  The timing runs on a PROBE env built from the same constructor arguments
         (same batch size, spawn table and seeds; destroyed afterwards), so this env's state, episode counters and statistics
-        are untouched: every candidate steps the probe 8 + `steps` times under uniform random actions between CUDA events
-        on the current stream, and the two best are measured again, interleaved.  Results do not depend on the shape
+        are untouched: every candidate steps the probe under uniform random actions, `steps` steps as one CUDA graph between
+        CUDA events, and the two best are measured again, interleaved.  Results do not depend on the shape
         (tests/test_cuda_env.py), only the time does -- the best shape depends on how the batch fills whole waves of the
         148 SMs.  Returns (ms per step, envs per CTA, threads per CTA, mode)."""
         if self._spawn_table is None:
@@ -158,14 +158,23 @@ class CattleHerdingBatchedEnv:
             probe.reset()
 
             def timed(g, th, mode, n):
+                # the n steps run as ONE CUDA graph: eager launches from Python cannot separate shapes that differ by 1-2 %
                 probe.set_launch(g, th)
                 probe.set_step_mode(mode)
-                for i in range(8):
-                    probe.step(act[i % 4], want_terminal_obs=False)
+                side = torch.cuda.Stream(device=self.device)
+                side.wait_stream(torch.cuda.current_stream(self.device))
+                with torch.cuda.stream(side):
+                    for i in range(8):
+                        probe.step(act[i % 4], want_terminal_obs=False)
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph, stream=side):
+                        for i in range(n):
+                            probe.step(act[i % 4], want_terminal_obs=False)
+                torch.cuda.current_stream(self.device).wait_stream(side)
+                graph.replay()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
-                for i in range(n):
-                    probe.step(act[i % 4], want_terminal_obs=False)
+                graph.replay()
                 e1.record()
                 e1.synchronize()
                 return e0.elapsed_time(e1) / n
