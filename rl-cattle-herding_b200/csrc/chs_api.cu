@@ -77,6 +77,8 @@ struct ChsHandle {
   int reg_variant;            // 0 auto, 1 latency (128 regs), 2 occupancy (64 regs)
   bool spawn_set;
   unsigned* amask;       // alpha-term in-range masks per spawn row (alpha_mask_kernel)
+  CUtensorMap tm_cpos, tm_cvel;   // fp32: herd tiles of the launch shape in use (configure_launch); valid when kp.tma_ok
+  bool knob_no_tma;      // CHS_NO_TMA=1: stage the herd with cp.async chunks (A/B runs)
   bool amask_ok;         // every env's cattle sit on its spawn row: a full reset happened and nobody injected positions
   // device-side buffers of the host path (allocated on first use)
   float *d_actions, *d_obs, *d_reward, *d_termobs;
@@ -146,6 +148,33 @@ static int smem_for(const ChsHandle* h, int G) {
 
 static const int kSmemCap = 200 * 1024;
 
+// Tensor map over one herd array seen as a row-major [M][2E] float matrix (row = cow, 2 floats per env), box = M rows x 2G
+// floats = the [cow][G] shared-memory tile of one CTA.  cuTensorMapEncodeTiled comes from the driver through the runtime
+// (no link against libcuda).  Returns false where TMA cannot express the tile (odd E, one env per CTA, more than 256 cows).
+typedef CUresult (*TmapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static bool herd_tensor_map(CUtensorMap* out, void* base, int E, int M, int G) {
+  static TmapEncodeFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (TmapEncodeFn)sym;
+    else
+      cudaGetLastError();
+  }
+  if (!fn || (E & 1) || G < 2 || M < 1 || M > 256) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)2 * (cuuint64_t)E, (cuuint64_t)M};
+  const cuuint64_t gstride[1] = {(cuuint64_t)E * 8u};
+  const cuuint32_t box[2] = {(cuuint32_t)(2 * G), (cuuint32_t)M};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static int configure_launch(ChsHandle* h, int gact, int threads) {
   // envs_per_block need not be a power of two: the shared-memory arrays keep a power-of-two stride G >= gact and the CTA
   // leaves the slots beyond gact empty.  An even count keeps the 16-byte async herd copies aligned.
@@ -178,6 +207,8 @@ static int configure_launch(ChsHandle* h, int gact, int threads) {
   h->kp.gact = gact;
   h->kp.lay = h->f64 ? layout_for<double>(h->kp, G) : layout_for<float>(h->kp, G);
   h->kp.cp_ok = h->f64 ? 1 : ((G >= 2 && (h->E & 1) == 0) ? 1 : 0);
+  h->kp.tma_ok = (!h->f64 && h->kp.cp_ok && !h->knob_no_tma && herd_tensor_map(&h->tm_cpos, h->cpos, h->E, h->kp.M, G) &&
+                  herd_tensor_map(&h->tm_cvel, h->cvel, h->E, h->kp.M, G)) ? 1 : 0;
   h->threads = threads;
   h->smem = smem;
   return CHS_OK;
@@ -267,6 +298,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   h->knob_full = getenv("CHS_FULL_KERNEL") != nullptr;
   kp.early_ok = getenv("CHS_NO_EARLY") ? 0 : 1;
   h->knob_deferred_reset = getenv("CHS_DEFERRED_RESET") != nullptr;
+  h->knob_no_tma = getenv("CHS_NO_TMA") != nullptr;
   h->knob_no_direct = getenv("CHS_NO_DIRECT") != nullptr;
   h->knob_no_pdl = getenv("CHS_NO_PDL") != nullptr;
   h->knob_host_copy = getenv("CHS_HOST_COPY") != nullptr;
@@ -447,6 +479,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.p = h->kp;
   a.drone = (typename VT<T>::v4*)h->drone; a.rpm = (typename VT<T>::v4*)h->rpm;
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
+  a.tm_cpos = h->tm_cpos; a.tm_cvel = h->tm_cvel;
   a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret; a.path = (T*)h->path;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats; a.tab = h->tab;
   a.amask = (h->amask_ok && !h->kp.cattle_integrate) ? h->amask : nullptr;

@@ -128,6 +128,27 @@ __device__ __forceinline__ void bulk_store_live(const KParams& p, const float* s
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_next() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ---- 2-D TMA tile load (global -> shared) completing on an mbarrier ----
+__device__ __forceinline__ void mbar_init(void* mbar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(mbar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(void* mbar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(mbar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, int x, int y, void* mbar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(tmap), "r"(x), "r"(y),
+                 "r"((unsigned)__cvta_generic_to_shared(mbar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void* mbar, unsigned parity) {
+  const unsigned addr = (unsigned)__cvta_generic_to_shared(mbar);
+  unsigned done = 0;
+  while (!done)
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.b32 %0, 1, 0, p; }"
+                 : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+}
+
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -572,8 +593,8 @@ __global__ void __launch_bounds__(256) drone_kernel(const KArgs<T> a) {
 // and bulk obs stores usable, no phase stamps): those branches are compiled out, which matters for batches of about
 // one wave where the kernel is bound by cold instruction fetch (tools/microbench/icache_cold.cu).
 template <typename T, int MAXT, int MINB, bool MARL, bool SPLIT, bool FULL>
-__global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+__global__ void __launch_bounds__(MAXT, MINB) step_kernel(const __grid_constant__ KArgs<T> a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   const KParams& p = a.p;
   Smem<T> s = carve<T>(smem_raw, p);
   const int t = threadIdx.x, nt = blockDim.x, G = p.G, E = p.E, D = p.D, M = p.M;
@@ -611,6 +632,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
   const int snt = nt - sw0, sw = t - sw0;    // sw < 0: exempt
   // prologue (no global memory): the observation staging area and the zero block are cleared while, under PDL, the
   // previous kernel of the stream is still draining
+  if (sizeof(T) == 4 && p.tma_ok && sw == 0) mbar_init(s.misc + 4, 1);
   if (sw >= 0) {
     const int nq = (G * p.stage_stride) >> 2;
     float4* st4 = reinterpret_cast<float4*>(s.stage);
@@ -660,7 +682,17 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       const int cpr = G / EPC;                             // chunks per cow row
       const int lcpr = ilog2_pow2(cpr);
       const int nchunk = 2 * M * cpr;
-      if (sw >= 0) for (int it = sw; it < nchunk; it += snt) {
+      if (sizeof(T) == 4 && p.tma_ok) {
+        // fp32: the whole [M][G] tile of positions and the one of velocities arrive through two TMA loads issued by one
+        // thread (box = M rows of G envs, out-of-range envs zero-filled by the unit); completion is counted on an mbarrier
+        // that the same thread waits on before the barrier that closes phase 0
+        if (sw == 0) {
+          void* mbar = s.misc + 4;
+          mbar_expect_tx(mbar, 2u * (unsigned)(M * G) * (unsigned)sizeof(V2));
+          tma_load_2d(s.cpos, &a.tm_cpos, 2 * e0, 0, mbar);
+          tma_load_2d(s.cvel, &a.tm_cvel, 2 * e0, 0, mbar);
+        }
+      } else if (sw >= 0) for (int it = sw; it < nchunk; it += snt) {
         const int arr = (it >= M * cpr) ? 1 : 0;
         const int r = it - arr * M * cpr;
         const int j = r >> lcpr, c = r & (cpr - 1);            // cpr is a power of two
@@ -701,6 +733,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const KArgs<T> a) {
       if (t == 0) { s.misc[0] = __popc(m); s.misc[1] = 0; s.misc[2] = (int)div_magic(__popc(m)); }
     }
     cp_async_wait_all();
+    if (sizeof(T) == 4 && p.tma_ok && (!FULL || p.cp_ok) && sw == 0) mbar_wait(s.misc + 4, 0);
   }
   CHS_STAMP(1);
   if (early) {

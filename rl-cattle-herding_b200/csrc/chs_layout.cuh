@@ -19,6 +19,7 @@
 //                          BaseAviary.py:1406-1435); negative = no step since the reset (the first step of an episode is
 //                          measured from the origin: last_drones_pos is zeroed by reset, :317)
 #pragma once
+#include <cuda.h>          // CUtensorMap (the type only: the encoder is fetched through cudaGetDriverEntryPoint)
 #include "chs_math.cuh"
 #include "../../include/chs.h"
 
@@ -59,6 +60,7 @@ struct KParams {
   int wrapper_quirks;    // MARL packing: outputs are those of the reference RLlib wrapper's second invocation (ChsParams.marl_wrapper_quirks)
   int late_rows;         // observations go to pinned host memory: live rows are stored after phase 3, finished envs skipped
   int gact;              // envs a CTA of the step kernel handles (<= G, the power-of-two shared-memory stride): wave fitting
+  int tma_ok;            // the herd tile of a CTA is fetched by two 2-D TMA loads (KArgs::tm_cpos / tm_cvel) instead of cp.async chunks
   int early_ok;          // warp 0 may start its drone chain before the other warps finish staging (CHS_NO_EARLY=1 clears it)
   uint32_t seed_lo, seed_hi;
   SmemLayout lay;        // = smem_layout<T>(D, M, G, stage_stride, zero_bytes): every thread of every CTA would recompute it otherwise
@@ -100,6 +102,10 @@ template <typename T> struct KArgs {
   int* dbg_neighbors;                // nullable [E][D][2]
   int* dbg_herded;                   // nullable [E]
   long long* dbg_clock;              // nullable [grid][32]: clock64() of thread 0 at phase and sub-phase boundaries
+  // fp32 build: tensor maps over cpos / cvel seen as [M][2E] floats, box = [M][2G]: one TMA load brings the herd positions (or
+  // velocities) of the G envs of a CTA into the [cow][G] shared-memory tile, zero-filled past the end of the batch
+  alignas(64) CUtensorMap tm_cpos;
+  alignas(64) CUtensorMap tm_cvel;
 };
 
 // ---- shared-memory carve-up (per CTA of G envs) ----------------------------------------------------
@@ -111,7 +117,9 @@ template <typename T> __host__ __device__ inline SmemLayout smem_layout(int D, i
   s.off_dpos = o; o += D * G * v4;
   s.off_redA = o; o += D * G * v4;
   s.off_redB = o; o += D * G * v4;
+  o = (o + 127) & ~127;                 // TMA destinations: 128-byte aligned
   s.off_cpos = o; o += M * G * v2;
+  o = (o + 127) & ~127;
   s.off_cvel = o; o += M * G * v2;
   s.off_u = o;    o += M * G * v2;
   o = (o + 15) & ~15;

@@ -203,11 +203,12 @@ def test_host_path_counts_and_terminal_rows_over_many_calls():
     env.close(); twin.close()
 
 
-@pytest.mark.parametrize("knob", ["CHS_NO_PDL", "CHS_HOST_COPY", "CHS_NO_DIRECT", "CHS_EARLY_ROWS", "CHS_DEFERRED_RESET"])
+@pytest.mark.parametrize("knob", ["CHS_NO_PDL", "CHS_HOST_COPY", "CHS_NO_DIRECT", "CHS_EARLY_ROWS", "CHS_DEFERRED_RESET", "CHS_NO_TMA"])
 def test_launch_and_host_path_knobs_do_not_change_results(knob, monkeypatch):
     """The step kernels are launched with programmatic dependent launch and the pinned host path is copy free; the knobs
     that turn either off (plain launches / results through the staging copy / everything staged in HBM), and the one that
-    moves split mode's rebuild of finished envs into a third kernel, are read at chs_create and must give the same bits: device path against device path, host path against host path, 30 steps with
+    moves split mode's rebuild of finished envs into a third kernel and the one that stages the herd with cp.async chunks
+    instead of TMA tile loads, are read at chs_create and must give the same bits: device path against device path, host path against host path, 30 steps with
     resets, fused and split."""
     E = 700
     rng = np.random.default_rng(5)
