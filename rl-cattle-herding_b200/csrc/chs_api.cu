@@ -54,6 +54,7 @@ struct ChsHandle {
   double* stats;
   double* tab;
   void* own2;
+  float* zero_page;      // 32 * stage_stride zero floats (KArgs::zero_page)
   void* pos0;
   int* done_list;
   int* done_count;
@@ -319,6 +320,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
   ALLOC0(h->drone, F_COUNT * D * E * 4 * ts);
   ALLOC0(h->rpm, D * E * 4 * ts);
   ALLOC0(h->cpos, M * E * 2 * ts);
+  ALLOC0(h->zero_page, (size_t)32 * kp.stage_stride * 4);
   ALLOC0(h->cvel, M * E * 2 * ts);
   ALLOC0(h->envf, E * sizeof(double2));
   ALLOC0(h->epret, E * sizeof(double));
@@ -380,7 +382,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
 extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
-  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->path, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->pos0, h->done_list, h->done_count, h->amask,
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->path, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->zero_page, h->pos0, h->done_list, h->done_count, h->amask,
                   h->d_actions, h->d_obs, h->d_small, h->d_termobs, h->d_mask, h->d_cta_done};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_small) cudaFreeHost(h->h_small);
@@ -479,7 +481,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.p = h->kp;
   a.drone = (typename VT<T>::v4*)h->drone; a.rpm = (typename VT<T>::v4*)h->rpm;
   a.cpos = (typename VT<T>::v2*)h->cpos; a.cvel = (typename VT<T>::v2*)h->cvel;
-  a.tm_cpos = h->tm_cpos; a.tm_cvel = h->tm_cvel;
+  a.tm_cpos = h->tm_cpos; a.tm_cvel = h->tm_cvel; a.zero_page = h->zero_page;
   a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret; a.path = (T*)h->path;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats; a.tab = h->tab;
   a.amask = (h->amask_ok && !h->kp.cattle_integrate) ? h->amask : nullptr;

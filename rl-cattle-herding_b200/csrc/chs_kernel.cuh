@@ -141,6 +141,12 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, in
                ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(tmap), "r"(x), "r"(y),
                  "r"((unsigned)__cvta_generic_to_shared(mbar)) : "memory");
 }
+// 1-D bulk (TMA) load global -> shared completing on an mbarrier; addresses and size are multiples of 16 bytes
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, unsigned bytes, void* mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes),
+                 "r"((unsigned)__cvta_generic_to_shared(mbar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(void* mbar, unsigned parity) {
   const unsigned addr = (unsigned)__cvta_generic_to_shared(mbar);
   unsigned done = 0;
@@ -632,11 +638,21 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const __grid_constant_
   const int snt = nt - sw0, sw = t - sw0;    // sw < 0: exempt
   // prologue (no global memory): the observation staging area and the zero block are cleared while, under PDL, the
   // previous kernel of the stream is still draining
-  if (sizeof(T) == 4 && p.tma_ok && sw == 0) mbar_init(s.misc + 4, 1);
+  const bool tma = sizeof(T) == 4 && p.tma_ok && (!FULL || p.cp_ok);
+  // Occupancy build (MINB > 1, batches of several waves, bound by instruction issue): the staging area is cleared and the
+  // curriculum table fetched by bulk copies as well -- two more instructions of one thread instead of loops over all of
+  // them (16 384 envs 23.3 -> 22.8 us, 65 536 fused 79.9 -> 77.4).  The latency build keeps the loops: its clearing runs in
+  // the PDL prologue, under the previous kernel's tail, and a one-wave launch whose CTAs all pull the same page of zeros
+  // through L2 at the same moment measured 1 % slower.
+  const bool tmaz = tma && MINB > 1;
+  const unsigned stage_bytes = (unsigned)(G * p.stage_stride) * 4u;
+  if (tma && sw == 0) mbar_init(s.misc + 4, 1);
   if (sw >= 0) {
-    const int nq = (G * p.stage_stride) >> 2;
-    float4* st4 = reinterpret_cast<float4*>(s.stage);
-    for (int i = sw; i < nq; i += snt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!tmaz) {
+      const int nq = (G * p.stage_stride) >> 2;
+      float4* st4 = reinterpret_cast<float4*>(s.stage);
+      for (int i = sw; i < nq; i += snt) st4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     for (int i = sw; i < (p.zero_bytes >> 4); i += snt) reinterpret_cast<float4*>(s.zeros)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   pdl_wait();
@@ -682,15 +698,19 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const __grid_constant_
       const int cpr = G / EPC;                             // chunks per cow row
       const int lcpr = ilog2_pow2(cpr);
       const int nchunk = 2 * M * cpr;
-      if (sizeof(T) == 4 && p.tma_ok) {
+      if (tma) {
         // fp32: the whole [M][G] tile of positions and the one of velocities arrive through two TMA loads issued by one
-        // thread (box = M rows of G envs, out-of-range envs zero-filled by the unit); completion is counted on an mbarrier
-        // that the same thread waits on before the barrier that closes phase 0
+        // thread (box = M rows of G envs, out-of-range envs zero-filled by the unit); completion is counted
+        // on an mbarrier that the same thread waits on before the barrier that closes phase 0
         if (sw == 0) {
           void* mbar = s.misc + 4;
-          mbar_expect_tx(mbar, 2u * (unsigned)(M * G) * (unsigned)sizeof(V2));
+          mbar_expect_tx(mbar, 2u * (unsigned)(M * G) * (unsigned)sizeof(V2) + (tmaz ? 76u * 16u + stage_bytes : 0u));
           tma_load_2d(s.cpos, &a.tm_cpos, 2 * e0, 0, mbar);
           tma_load_2d(s.cvel, &a.tm_cvel, 2 * e0, 0, mbar);
+          if (tmaz) {
+            bulk_load(s.ctab, a.tab, 76u * 16u, mbar);
+            bulk_load(s.stage, a.zero_page, stage_bytes, mbar);
+          }
         }
       } else if (sw >= 0) for (int it = sw; it < nchunk; it += snt) {
         const int arr = (it >= M * cpr) ? 1 : 0;
@@ -711,7 +731,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const __grid_constant_
       }
     }
     // curriculum table: 76 chunks of 16 bytes
-    if (sw >= 0) for (int it = sw; it < 76; it += snt) cp_async16(s.ctab + 2 * it, a.tab + 2 * it, 16);
+    if (sw >= 0 && !tmaz) for (int it = sw; it < 76; it += snt) cp_async16(s.ctab + 2 * it, a.tab + 2 * it, 16);
     cp_async_commit();
     pdl_launch_next();        // every load of this step is in flight: the next kernel of the stream may start its prologue
     if (FULL && !p.cp_ok) {
@@ -733,7 +753,7 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const __grid_constant_
       if (t == 0) { s.misc[0] = __popc(m); s.misc[1] = 0; s.misc[2] = (int)div_magic(__popc(m)); }
     }
     cp_async_wait_all();
-    if (sizeof(T) == 4 && p.tma_ok && (!FULL || p.cp_ok) && sw == 0) mbar_wait(s.misc + 4, 0);
+    if (tma && sw == 0) mbar_wait(s.misc + 4, 0);
   }
   CHS_STAMP(1);
   if (early) {

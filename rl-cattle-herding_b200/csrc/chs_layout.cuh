@@ -83,6 +83,7 @@ template <typename T> struct KArgs {
   const unsigned* amask;             // nullable [n_sims][M][ceil(M/32)]: alpha-term in-range masks per spawn row (chs_flock.cuh)
   double* stats;                     // [CHS_STAT_ROWS][CHS_NUM_STATS], row = CTA index mod CHS_STAT_ROWS
   const double* tab;                 // [CHS_TAB_DOUBLES] curriculum rows + 1/n (chs_task.cuh)
+  const float* zero_page;            // 32 * stage_stride zero floats: source of the bulk copy that clears a CTA's obs staging area (occupancy build)
   // per-call
   const float* actions;              // [E][D][A]
   float* obs;                        // [E][R][L]
