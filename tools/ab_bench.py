@@ -2,7 +2,7 @@
 them (rotating batches larger than L2, one CUDA graph of K steps, one event pair), for the library named by CHS_LIB.
     CHS_LIB=/path/libchs_variant.so python tools/ab_bench.py [head] [c3] [mid] [c4] [big]
 Launch shapes: the ones bench.py's autotune settles on (fixed here so that variants are compared like for like) unless
-AB_SHAPES="G,T;G,T" overrides the launch shapes of every case named, AB_MODE=fused|split the step mode, AB_ENVS the batch size."""
+AB_SHAPES="G,T;G,T" overrides the launch shapes of every case named, AB_MODE=fused|split the step mode, AB_ENVS the batch size, AB_VARIANT=1|2 the register build."""
 import os
 import sys
 
@@ -31,6 +31,9 @@ for name in what:
     for g, th in shapes:
         try:
             rot.configure(g, th, mode)
+            if os.environ.get("AB_VARIANT"):       # 1 = latency build (128 registers), 2 = occupancy build (64)
+                for env in rot.envs:
+                    pkg._lib.check(env.lib.chs_set_register_variant(env._h, int(os.environ["AB_VARIANT"])))
         except RuntimeError as exc:
             print(f"{tag} {name} G={g} T={th}: {exc}")
             continue
