@@ -178,7 +178,9 @@ static bool herd_tensor_map(CUtensorMap* out, void* base, int E, int M, int G) {
 
 static int configure_launch(ChsHandle* h, int gact, int threads) {
   // envs_per_block need not be a power of two: the shared-memory arrays keep a power-of-two stride G >= gact and the CTA
-  // leaves the slots beyond gact empty.  An even count keeps the 16-byte async herd copies aligned.
+  // leaves the slots beyond gact empty.  An even count keeps the first env of every CTA on a 16-byte boundary of the herd rows:
+  // the async 16-byte copies need it, and so do the TMA tile loads (a box that starts 8 bytes off raises "illegal
+  // instruction" on the B200 -- measured with 7 envs per CTA).
   if (gact < 1 || gact > 32) return fail(CHS_ERR_INVALID, "envs_per_block must be in 1..32");
   int G = 1;
   while (G < gact) G <<= 1;
