@@ -82,6 +82,45 @@ __device__ __forceinline__ void alpha_term(const typename VT<T>::v2* s_cpos, con
   uy = T(k::C2_ALPHA) * gy + T(k::C2_ALPHA) * cy;
 }
 
+// Weights of lattice_term without the accumulation: gradient weight `w` and consensus weight `b` of one displacement.
+template <typename T>
+__device__ __forceinline__ void lattice_weights(T dx, T dy, T sigma_r, T inv_sigma_r, T& w, T& b) {
+  const T r2 = dx * dx + dy * dy;
+  const T q = T(1) + T(k::EPS) * r2;
+  const T rs = Mth<T>::rsqrt(q);
+  const T sn = r2 * Mth<T>::frcp(q * rs + T(1));
+  b = bump<T>(sn * inv_sigma_r);
+  const T zz = sn - sigma_r;
+  w = b * T(k::PHI_HALF_AB) * zz * Mth<T>::rsqrt(T(1) + zz * zz) * rs;
+}
+
+// alpha term from the per-spawn-row WEIGHT table (chs_set_spawn_table: alpha_weight_kernel).  Cattle never move on the DYN
+// path, so for a herd that sits on its spawn row everything in the alpha term that depends on positions only is a constant
+// of (row, cow): the whole gradient sum, and the bump weight of every in-range neighbour.  What is left per neighbour is
+// the consensus piece b * (p_j - p_i) with the live velocities: 2 FMAs instead of four MUFU operations and ~40 instructions.
+// Neighbours are walked in mask order, the order the table was filled in, so the sums are those of alpha_term.
+template <typename T>
+__device__ __forceinline__ void alpha_term_tab(const typename VT<T>::v2* s_cvel, int i, int g, int G, int M,
+                                               const unsigned* __restrict__ mwords, typename VT<T>::v2 grad,
+                                               const T* __restrict__ wts, T& ux, T& uy) {
+  const auto pi = s_cvel[i * G + g];
+  T cx = 0, cy = 0;
+  int kk = 0;
+  for (int j0 = 0; j0 < M; j0 += 32) {
+    unsigned mask = __ldg(mwords + (j0 >> 5));
+    while (mask) {
+      const int j = j0 + __ffs(mask) - 1;
+      mask &= mask - 1;
+      const T b = __ldg(wts + kk);
+      ++kk;
+      const auto pj = s_cvel[j * G + g];
+      cx += b * (pj.x - pi.x); cy += b * (pj.y - pi.y);
+    }
+  }
+  ux = T(k::C2_ALPHA) * grad.x + T(k::C2_ALPHA) * cx;
+  uy = T(k::C2_ALPHA) * grad.y + T(k::C2_ALPHA) * cy;
+}
+
 // alpha_term for herds of more than 32 cows with the mask table: the first four mask words (up to 128 cows) are fetched
 // together, one L2 round trip instead of one per 32-cow chunk (the loads of the plain version are serialised by the walk over
 // each chunk's set bits).  Out of line on purpose: the small-herd kernels are sensitive to every instruction added to their

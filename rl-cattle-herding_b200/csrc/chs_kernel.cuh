@@ -494,6 +494,41 @@ __global__ void __launch_bounds__(256) alpha_mask_kernel(const typename VT<T>::v
     out[(size_t)idx * nch + c] = alpha_chunk_mask<T>([&](int j) { return r[j]; }, qi, i, c * 32, M);
 }
 
+// Position-only part of the alpha term of every cow of every spawn row (one thread per (row, cow)): gradient sum and the
+// consensus weight of each in-range neighbour, walked in the order of the mask table with lattice_term's own arithmetic.
+// `*max_cnt` receives the largest neighbour count when `grad` is null (first pass, sizes the weight rows).
+template <typename T>
+__global__ void __launch_bounds__(256) alpha_weight_kernel(const typename VT<T>::v2* spawn, int n_sims, int stride, int M,
+                                                           const unsigned* masks, typename VT<T>::v2* grad, T* wts, int wstride,
+                                                           int* max_cnt) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_sims * M) return;
+  const int row = idx / M, i = idx - row * M, nch = (M + 31) >> 5;
+  const typename VT<T>::v2* r = spawn + (size_t)row * stride;
+  const auto qi = r[i];
+  T gx = 0, gy = 0, cx = 0, cy = 0;
+  int kk = 0;
+  for (int c = 0; c < nch; ++c) {
+    unsigned mask = masks[(size_t)idx * nch + c];
+    while (mask) {
+      const int j = c * 32 + __ffs(mask) - 1;
+      mask &= mask - 1;
+      if (grad) {
+        const auto qj = r[j];
+        // the gradient sum grows through lattice_term itself (the step kernel's arithmetic); the consensus weight is
+        // lattice_term's `b`, taken from the same expressions
+        lattice_term<T>(qj.x - qi.x, qj.y - qi.y, T(0), T(0), T(k::SIGMA_ALPHA), T(1.0 / k::SIGMA_ALPHA), gx, gy, cx, cy);
+        T w, b;
+        lattice_weights<T>(qj.x - qi.x, qj.y - qi.y, T(k::SIGMA_ALPHA), T(1.0 / k::SIGMA_ALPHA), w, b);
+        wts[(size_t)idx * wstride + kk] = b;
+      }
+      ++kk;
+    }
+  }
+  if (grad) grad[idx] = mk2<T>(gx, gy);
+  else atomicMax(max_cnt, kk);
+}
+
 // After a state injection: do the herd positions of every env still equal its spawn row bit for bit?  (Then the
 // alpha-range table stays valid.)  One thread per (cow, env); *bad counts the mismatches.
 template <typename T>
@@ -903,7 +938,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const __grid_constant_
         const int g = s.flist[slot];
         T ux, uy;
         const unsigned* mw = a.amask ? a.amask + ((size_t)s.row[g] * M + i) * ((M + 31) >> 5) : nullptr;
-        if (mw && M > 32) { T u2[2]; alpha_term_wide<T>(s.cpos, s.cvel, i, g, G, M, mw, u2); ux = u2[0]; uy = u2[1]; }
+        if (mw && a.aw) {
+          const size_t rc = (size_t)s.row[g] * M + i;
+          alpha_term_tab<T>(s.cvel, i, g, G, M, mw, a.agrad[rc], a.aw + rc * a.aw_stride, ux, uy);
+        } else if (mw && M > 32) { T u2[2]; alpha_term_wide<T>(s.cpos, s.cvel, i, g, G, M, mw, u2); ux = u2[0]; uy = u2[1]; }
         else alpha_term<T>(s.cpos, s.cvel, i, g, G, M, mw, ux, uy);
         s.u[i * G + g] = mk2<T>(ux, uy);
       }

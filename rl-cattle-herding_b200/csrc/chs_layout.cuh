@@ -81,6 +81,11 @@ template <typename T> struct KArgs {
   T* path;                           // [D][E] running 1.7 x path length per drone (BaseAviary.py:1424), < 0 = fresh episode
   const typename VT<T>::v2* spawn;   // [n_sims][spawn_stride]
   const unsigned* amask;             // nullable [n_sims][M][ceil(M/32)]: alpha-term in-range masks per spawn row (chs_flock.cuh)
+  // nullable, valid with amask: per (spawn row, cow) the alpha term's position-only part -- .x/.y = sum of the gradient pieces,
+  // and aw[(row * M + cow) * aw_stride + k] = consensus weight (the bump value) of its k-th in-range neighbour in mask order
+  const typename VT<T>::v2* agrad;
+  const T* aw;
+  int aw_stride;
   double* stats;                     // [CHS_STAT_ROWS][CHS_NUM_STATS], row = CTA index mod CHS_STAT_ROWS
   const double* tab;                 // [CHS_TAB_DOUBLES] curriculum rows + 1/n (chs_task.cuh)
   const float* zero_page;            // 32 * stage_stride zero floats: source of the bulk copy that clears a CTA's obs staging area (occupancy build)

@@ -68,8 +68,11 @@ def test_edge_shapes_against_oracle(case, mode):
 
 @pytest.mark.parametrize("shape", [(3, 20), (8, 100), (4, 33)], ids=lambda s: "D%d_M%d" % s)
 def test_alpha_range_table_equals_computed_ranges(shape, monkeypatch):
-    """The per-spawn-row table of alpha-term in-range masks (built by chs_set_spawn_table) against the distance pass it
-    replaces: same herd velocities, bit for bit, over free-running steps with resets in between."""
+    """The per-spawn-row tables of the alpha term (built by chs_set_spawn_table) against the distance pass they replace, over
+    free-running steps with resets in between.  The in-range MASKS alone give the same herd velocities bit for bit.  With the
+    WEIGHT table the gradient sum of a cow is precomputed by another kernel (same expressions, another compilation: fp32
+    contraction may differ in the last bit), so velocities agree to rounding; everything a step returns is still bit-equal
+    (the herd does not move on the DYN path, so velocities feed nothing back)."""
     import rl_cattle_herding_b200 as pkg
     D, M = shape
     E = 64
@@ -78,19 +81,26 @@ def test_alpha_range_table_equals_computed_ranges(shape, monkeypatch):
     def make():
         return pkg.CattleHerdingBatchedEnv(E, num_drones=D, num_cattle=M, ctrl_freq=30, fixed_num_drones=D, spawn_table=table,
                                            device=0, seed=9, auto_reset=True)
+    with_weights = make()
+    monkeypatch.setenv("CHS_NO_ALPHA_WEIGHTS", "1")     # both read by chs_set_spawn_table
     with_table = make()
-    monkeypatch.setenv("CHS_NO_ALPHA_TABLE", "1")       # read by chs_set_spawn_table
+    monkeypatch.setenv("CHS_NO_ALPHA_TABLE", "1")
     computed = make()
     monkeypatch.delenv("CHS_NO_ALPHA_TABLE")
-    for env in (with_table, computed):
+    monkeypatch.delenv("CHS_NO_ALPHA_WEIGHTS")
+    for env in (with_weights, with_table, computed):
         env.reset()
     gen = torch.Generator("cuda").manual_seed(2)
     for t in range(40):
         act = torch.rand((E, D, 4), device="cuda", generator=gen) * 2 - 1
         a = [x.clone() for x in with_table.step(act)]
+        w = [x.clone() for x in with_weights.step(act)]
         b = computed.step(act)
         assert all(torch.equal(x, y) for x, y in zip(a, b)), t
-    sa, sb = with_table.get_state(), computed.get_state()
+        assert all(torch.equal(x, y) for x, y in zip(w, b)), t
+    sa, sw, sb = with_table.get_state(), with_weights.get_state(), computed.get_state()
     assert np.array_equal(sa["cattle_vel"], sb["cattle_vel"]) and np.array_equal(sa["cattle_pos"], sb["cattle_pos"])
+    assert np.array_equal(sw["cattle_pos"], sb["cattle_pos"])
+    assert np.allclose(sw["cattle_vel"], sb["cattle_vel"], rtol=0, atol=2e-6), np.abs(sw["cattle_vel"] - sb["cattle_vel"]).max()
     assert with_table.stats()[0] > 0          # episodes ended and restarted on other spawn rows along the way
-    with_table.close(); computed.close()
+    with_weights.close(); with_table.close(); computed.close()
