@@ -78,7 +78,7 @@ struct ChsHandle {
   int reg_variant;            // 0 auto, 1 latency (128 regs), 2 occupancy (64 regs)
   bool spawn_set;
   unsigned* amask;       // alpha-term in-range masks per spawn row (alpha_mask_kernel)
-  void* agrad; void* aw; int aw_stride;   // alpha-term weight table per spawn row (alpha_weight_kernel), valid with amask
+  void* agrad; void* aw; int aw_stride; double2* acent;   // alpha-term weight table per spawn row (alpha_weight_kernel), valid with amask
   CUtensorMap tm_cpos, tm_cvel;   // fp32: herd tiles of the launch shape in use (configure_launch); valid when kp.tma_ok
   bool knob_no_tma;      // CHS_NO_TMA=1: stage the herd with cp.async chunks (A/B runs)
   bool amask_ok;         // every env's cattle sit on its spawn row: a full reset happened and nobody injected positions
@@ -385,7 +385,7 @@ extern "C" int chs_create(const ChsParams* prm, int32_t num_envs, int32_t device
 extern "C" int chs_destroy(ChsHandle* h) {
   if (!h) return CHS_OK;
   DeviceGuard dg(h->device);
-  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->path, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->zero_page, h->pos0, h->done_list, h->done_count, h->amask, h->agrad, h->aw,
+  void* ptrs[] = {h->drone, h->rpm, h->cpos, h->cvel, h->envf, h->epret, h->path, h->spawn, h->envi, h->envj, h->stats, h->tab, h->own2, h->zero_page, h->pos0, h->done_list, h->done_count, h->amask, h->agrad, h->aw, h->acent,
                   h->d_actions, h->d_obs, h->d_small, h->d_termobs, h->d_mask, h->d_cta_done};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_small) cudaFreeHost(h->h_small);
@@ -432,6 +432,7 @@ extern "C" int chs_set_spawn_table(ChsHandle* h, const double* xy, int32_t n_sim
   if (h->amask) { cudaFree(h->amask); h->amask = nullptr; }
   if (h->agrad) { cudaFree(h->agrad); h->agrad = nullptr; }
   if (h->aw) { cudaFree(h->aw); h->aw = nullptr; }
+  if (h->acent) { cudaFree(h->acent); h->acent = nullptr; }
   h->amask_ok = false;                 // until the next full reset puts every herd on its row of the new table
   const size_t words = (size_t)n_sims * h->kp.M * ((h->kp.M + 31) / 32);
   if (h->kp.M > 0 && !getenv("CHS_NO_ALPHA_TABLE") && words * sizeof(unsigned) <= (64u << 20)) {
@@ -443,6 +444,9 @@ extern "C" int chs_set_spawn_table(ChsHandle* h, const double* xy, int32_t n_sim
     // ... and so is everything in the alpha term that depends on positions only: the gradient sum and the consensus weight
     // of every in-range neighbour (chs_flock.cuh: alpha_term_tab).  First pass sizes the weight rows, second pass fills them.
     if (!getenv("CHS_NO_ALPHA_WEIGHTS")) {
+      CUDA_TRY(cudaMalloc(&h->acent, (size_t)n_sims * sizeof(double2)));
+      if (h->f64) spawn_centroid_kernel<double><<<(n_sims + 127) / 128, 128>>>((const double2*)h->spawn, n_sims, cows_per_sim, h->kp.M, h->acent);
+      else        spawn_centroid_kernel<float><<<(n_sims + 127) / 128, 128>>>((const float2*)h->spawn, n_sims, cows_per_sim, h->kp.M, h->acent);
       int* dmax = nullptr;
       int hmax = 0;
       CUDA_TRY(cudaMalloc(&dmax, sizeof(int)));
@@ -513,6 +517,7 @@ template <typename T> static KArgs<T> base_args(ChsHandle* h) {
   a.envi = h->envi; a.envj = h->envj; a.envf = (double2*)h->envf; a.epret = (double*)h->epret; a.path = (T*)h->path;
   a.spawn = (const typename VT<T>::v2*)h->spawn; a.stats = h->stats; a.tab = h->tab;
   a.amask = (h->amask_ok && !h->kp.cattle_integrate) ? h->amask : nullptr;
+  if (a.amask && h->acent) a.acent = h->acent;
   if (a.amask && h->aw) { a.agrad = (const typename VT<T>::v2*)h->agrad; a.aw = (const T*)h->aw; a.aw_stride = h->aw_stride; }
   a.own2 = (typename VT<T>::v4*)h->own2; a.pos0 = (const typename VT<T>::v4*)h->pos0;
   a.dbg_neighbors = h->dbg_nb; a.dbg_herded = h->dbg_herd; a.dbg_clock = h->dbg_clock;

@@ -529,6 +529,31 @@ __global__ void __launch_bounds__(256) alpha_weight_kernel(const typename VT<T>:
   else atomicMax(max_cnt, kk);
 }
 
+// Herd centroid of every spawn row (one thread per row) in the summation order of the step kernel: a serial pass for herds
+// under 48 cows, 8 strided partial sums folded by an xor tree for larger ones (centroid_wide).
+template <typename T>
+__global__ void __launch_bounds__(128) spawn_centroid_kernel(const typename VT<T>::v2* spawn, int n_sims, int stride, int M, double2* out) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= n_sims) return;
+  const typename VT<T>::v2* r = spawn + (size_t)row * stride;
+  const double inv_m = 1.0 / (double)M;
+  if (M < 48) {
+    double cx = 0, cy = 0;
+    for (int j = 0; j < M; ++j) { cx += (double)r[j].x; cy += (double)r[j].y; }
+    out[row] = make_double2(cx * inv_m, cy * inv_m);
+  } else {
+    double sx[8], sy[8];
+    for (int sub = 0; sub < 8; ++sub) {
+      double cx = 0, cy = 0;
+      for (int j = sub; j < M; j += 8) { cx += (double)r[j].x; cy += (double)r[j].y; }
+      sx[sub] = cx; sy[sub] = cy;
+    }
+    for (int o = 4; o > 0; o >>= 1)
+      for (int k = 0; k < o; ++k) { sx[k] += sx[k + o]; sy[k] += sy[k + o]; }     // lane k of the tree adds its partner k ^ o
+    out[row] = make_double2(sx[0] * inv_m, sy[0] * inv_m);
+  }
+}
+
 // After a state injection: do the herd positions of every env still equal its spawn row bit for bit?  (Then the
 // alpha-range table stays valid.)  One thread per (cow, env); *bad counts the mismatches.
 template <typename T>
@@ -924,8 +949,10 @@ __global__ void __launch_bounds__(MAXT, MINB) step_kernel(const __grid_constant_
       // made the first G worker threads the last to reach the barrier (4000 cycles, measured with the lean-build stamps;
       // config 3: 17.4 -> 16.2 us), while for 20 cows the tree costs more instructions than it saves latency.  Either way
       // the summation order depends on M only, not on the launch shape or the step mode.
-      const bool wide_herd = M >= 48;
-      if (!wide_herd && w < G) {
+      const bool wide_herd = M >= 48 && !a.acent;
+      if (a.acent) {
+        if (w < G) s.ccent[w] = a.acent[s.row[w]];      // a property of the spawn row while the herd sits on it
+      } else if (!wide_herd && w < G) {
         double cx = 0, cy = 0;
 #pragma unroll 4
         for (int j = 0; j < M; ++j) { const auto c = s.cpos[j * G + w]; cx += (double)c.x; cy += (double)c.y; }

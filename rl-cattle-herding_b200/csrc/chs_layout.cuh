@@ -86,6 +86,7 @@ template <typename T> struct KArgs {
   const typename VT<T>::v2* agrad;
   const T* aw;
   int aw_stride;
+  const double2* acent;              // nullable, valid with amask: herd centroid of every spawn row (float64, the step kernel's summation order)
   double* stats;                     // [CHS_STAT_ROWS][CHS_NUM_STATS], row = CTA index mod CHS_STAT_ROWS
   const double* tab;                 // [CHS_TAB_DOUBLES] curriculum rows + 1/n (chs_task.cuh)
   const float* zero_page;            // 32 * stage_stride zero floats: source of the bulk copy that clears a CTA's obs staging area (occupancy build)
